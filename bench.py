@@ -1,0 +1,361 @@
+#!/usr/bin/env python
+"""Benchmark of the rigid-resample hot path (BASELINE.json metric: resampled Gvoxel/s, % of HBM roofline).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--no-extra]
+
+N > 1 is launched by torchrun, one rank per GPU.  A "step" is one pass of the hot path over one volume:
+BASELINE config 2 -- synthetic CT 512x512x300 int16, general rigid (3,-2,4 deg; 5,-3,7 mm), resampled exactly
+as ``Rigid.create_image`` does (VTK mode, auto-cropped lattice, background -3001).  Each rank resamples its own
+volume (weak scaling; the batch-of-volumes sharding of config 4), no data-path collective.
+Rank 0 prints ONE JSON line.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from medicalimageanalysis_b200 import geometry as G                  # noqa: E402
+from medicalimageanalysis_b200.phantom import make_phantom            # noqa: E402
+
+SHAPE = (300, 512, 512)                       # [z, y, x]  BASELINE config 2
+SPACING = (0.9765625, 0.9765625, 2.5)
+GT = (3.0, -2.0, 4.0, 5.0, -3.0, 7.0)
+WORKLOAD = "C2: synthetic CT 512x512x300 int16, rigid (3,-2,4 deg; 5,-3,7 mm) resample, VTK-mode auto-crop"
+METRIC = "resampled_output_voxels_per_second"
+UNIT = "Gvoxel/s"
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def workload_geometry():
+    grid = G.Grid((SHAPE[2], SHAPE[1], SHAPE[0]), SPACING,
+                  tuple(-0.5 * np.array(SPACING) * np.array(SHAPE[::-1])))
+    M = G.params_to_matrix(GT, (0.0, 0.0, 0.0))
+    origin, dims = G.autocrop_extent(grid, M, SPACING, convention="vtk")
+    out_grid = G.Grid(dims, SPACING, origin)
+    A = G.compose_index_matrix(out_grid, grid, M, convention="vtk")
+    return grid, A, dims
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.gpu, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_reslice_runs(mov, A, dims, runs):
+    """The CPU arm: this repo's C/OpenMP restatement of the reference path (oracle/csrc/oracle_omp.c), all host
+    threads.  (VTK / SimpleITK, the reference's real native code, are not installable in this image.)"""
+    from oracle import native
+    native.build()
+    threads = native.set_threads(0)
+    nvox = dims[0] * dims[1] * dims[2]
+    native.reslice(mov, A, dims, -3001.0, "vtk")          # warm-up (page faults, thread pool)
+    times = []
+    for _ in range(runs):
+        t0 = time.perf_counter()
+        native.reslice(mov, A, dims, -3001.0, "vtk")
+        times.append(time.perf_counter() - t0)
+    return nvox, times, threads
+
+
+def run_reference(args, rank):
+    """--impl reference: the CPU implementation of the path on the box's host cores."""
+    if rank != 0:
+        return
+    grid, A, dims = workload_geometry()
+    mov = make_phantom(SHAPE, "CT", seed=2, spacing=SPACING)
+    runs = max(1, args.steps)
+    nvox, times, threads = cpu_reslice_runs(mov, A, dims, runs + 0)
+    total = sum(times)
+    value = nvox * len(times) / total / 1e9
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": len(times), "warmup": 1, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64 interpolation, i16 storage", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "out_dims_xyz": list(dims)},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": "full %dx%dx%d output volume per step, %d steps" % (dims + (len(times),))},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def extras(dev, torch, kernels, peak):
+    """Secondary measurements of the same path (not the headline): FFS permutation, fused SSD with store
+    (config 1), and the CT->MR MI registration loop (config 3)."""
+    from medicalimageanalysis_b200 import Data, RegistrationConfig
+    from medicalimageanalysis_b200.utils import CreateImageFromMask
+    from medicalimageanalysis_b200.utils import rigid as R
+    out = {}
+
+    def time_launches(fn, n=20, warm=3):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize(dev)
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n)]
+        for a, b in ev:
+            a.record(); fn(); b.record()
+        torch.cuda.synchronize(dev)
+        return statistics.median(a.elapsed_time(b) for a, b in ev) * 1e-3
+
+    # FFS permutation of the C2 volume (exact copy, 4 B / voxel)
+    vols = [torch.randint(-1024, 3071, SHAPE, device=dev, dtype=torch.int16) for _ in range(2)]
+    outs = [torch.empty((SHAPE[0], SHAPE[2], SHAPE[1]), device=dev, dtype=torch.int16) for _ in range(2)]
+    state = {"i": 0}
+    for case in ("axial_k1", "axial_k2", "axial_k3"):
+        perm, flip = kernels.FFS_PERMUTATIONS[case]
+
+        def fn():
+            i = state["i"] = (state["i"] + 1) % 2
+            kernels.permute_axes(vols[i], perm, flip, out=outs[i].view(tuple(vols[i].shape[p] for p in perm)))
+        t = time_launches(fn)
+        nv = vols[0].numel()
+        out["ffs_" + case] = {"gvoxel_s": nv / t / 1e9, "hbm_frac": 4.0 * nv / t / 1e9 / peak, "us": t * 1e6}
+    del vols, outs
+
+    # config 1: CT 512x512x100, one resample + SSD with store (6 B / voxel)
+    shape1 = (100, 512, 512)
+    g1 = G.Grid((512, 512, 100), SPACING, tuple(-0.5 * np.array(SPACING) * np.array(shape1[::-1])))
+    M = G.params_to_matrix(GT, (0.0, 0.0, 0.0))
+    A1 = G.compose_index_matrix(g1, g1, M)
+    f1 = torch.from_numpy(make_phantom(shape1, "CT", seed=1, spacing=SPACING)).to(dev)
+    m1 = torch.from_numpy(make_phantom(shape1, "CT", seed=1, spacing=SPACING, world_matrix=np.linalg.inv(M))).to(dev)
+    o1 = torch.empty_like(m1)
+    ws = kernels.MetricWorkspace(dev, n_mats=13)
+    t = time_launches(lambda: kernels.resample_ssd(f1, m1, A=A1, mode="itk", ws=ws, out=o1))
+    out["c1_resample_ssd_store"] = {"gvoxel_s": f1.numel() / t / 1e9, "hbm_frac": 6.0 * f1.numel() / t / 1e9 / peak,
+                                   "us": t * 1e6}
+    t = time_launches(lambda: kernels.resample_ssd(f1, m1, A=A1, mode="itk", ws=ws))
+    out["c1_ssd_evaluate"] = {"gvoxel_s": f1.numel() / t / 1e9, "hbm_frac": 4.0 * f1.numel() / t / 1e9 / peak,
+                              "us": t * 1e6}
+    del f1, m1, o1
+
+    # config 3: CT -> MR 256^3 float32, joint-histogram MI registration loop, 200 iterations, 13 probes each
+    shape3, sp3 = (256, 256, 256), (1.0, 1.0, 1.0)
+    gt3 = (4.0, 3.0, -5.0, 6.0, -4.0, 3.0)
+    Data.clear()
+    fixed = make_phantom(shape3, "CT", seed=3, spacing=sp3).astype(np.float32)
+    f3 = CreateImageFromMask(fixed, (-128.0, -128.0, -128.0), sp3, "fixed", device=dev).add_image()
+    M3 = G.params_to_matrix(gt3, f3.compute_center())
+    moving = make_phantom(shape3, "MR", seed=3, spacing=sp3, world_matrix=np.linalg.inv(M3))
+    m3 = CreateImageFromMask(moving, (-128.0, -128.0, -128.0), sp3, "moving", device=dev).add_image()
+    for metric in ("mi", "ssd"):
+        cfg = RegistrationConfig(metric=metric, iterations=200, bins=64, graph_iters=10)
+        R.register_rigid(f3, m3, cfg=RegistrationConfig(metric=metric, iterations=20, bins=64, graph_iters=10))
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        res = R.register_rigid(f3, m3, cfg=cfg)
+        torch.cuda.synchronize(dev)
+        dt = time.perf_counter() - t0
+        nv = f3.array.numel()
+        out["c3_register_" + metric] = {
+            "iters_per_s": res.iterations / dt, "evals_per_s": res.evaluations / dt,
+            "hbm_frac_per_eval": 8.0 * nv * res.evaluations / dt / 1e9 / peak,
+            "final_params": [round(float(x), 3) for x in res.params], "gt_params": list(gt3),
+            "cost_first": float(res.cost_history[0]), "cost_last": float(res.cost_history[-1])}
+    Data.clear()
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-extra", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from medicalimageanalysis_b200 import kernels
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    peak, peak_kind = measured_peak()
+    W, K = max(3, args.warmup), max(1, args.steps)
+
+    grid, A, dims = workload_geometry()
+    oshape = (dims[2], dims[1], dims[0])
+    nvox_out = dims[0] * dims[1] * dims[2]
+    nvox_in = SHAPE[0] * SHAPE[1] * SHAPE[2]
+    mov_h = make_phantom(SHAPE, "CT", seed=2 + rank, spacing=SPACING)
+    # ring of 3 input / output buffers (about 1 GB): nothing can stay in the 126 MB L2 between steps
+    ring = 3
+    movs = [torch.from_numpy(mov_h).to(dev) for _ in range(ring)]
+    outs = [torch.empty(oshape, dtype=torch.int16, device=dev) for _ in range(ring)]
+
+    def step(i):
+        kernels.resample(movs[i % ring], A, oshape, background=-3001.0, mode="vtk", out=outs[i % ring])
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for i in range(W):
+        step(i)
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for i in range(K):
+        ev[i][0].record()
+        step(i)
+        ev[i][1].record()
+    e1.record()
+    barrier()
+    total_ms = e0.elapsed_time(e1)
+    kernel_ms = [a.elapsed_time(b) for a, b in ev]
+    # keep the GPU busy a little longer so the clock sampler sees load even for a very short timed region
+    t_end = time.perf_counter() + 0.6
+    i = 0
+    while time.perf_counter() < t_end:
+        step(i); i += 1
+        if i % 50 == 0:
+            torch.cuda.synchronize(dev)
+    torch.cuda.synchronize(dev)
+    clocks = sampler.stop()
+
+    # ---- end to end through the host-buffer C-ABI entry point: pinned host in, pinned host out ----
+    pin_in = kernels.pinned_empty(SHAPE, np.int16)
+    pin_in[...] = mov_h
+    pin_out = kernels.pinned_empty(oshape, np.int16)
+    Ke = max(3, min(K, 10))
+    for _ in range(2):
+        kernels.resample_host(pin_in, A, oshape, mode="vtk", out=pin_out, device=local_rank)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(Ke):
+        kernels.resample_host(pin_in, A, oshape, mode="vtk", out=pin_out, device=local_rank)
+        _ = int(pin_out[0, 0, 0])            # the result is read on the host every step
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    check = int(np.abs(pin_out.astype(np.int32) - outs[(K - 1) % ring].cpu().numpy().astype(np.int32)).max()) \
+        if rank == 0 else 0
+
+    tm = torch.tensor([total_ms, e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+    total_ms, e2e_s = float(tm[0]), float(tm[1])
+
+    if rank == 0:
+        value = world * nvox_out * K / (total_ms * 1e-3) / 1e9
+        kavg = statistics.mean(kernel_ms) * 1e-3
+        alg_bytes = 2.0 * nvox_in + 2.0 * nvox_out          # N_m*b_m + N_o*b_o, int16 both
+        achieved = alg_bytes / kavg / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 interpolation (f64 row origin), i16 storage", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "in_dims_xyz": [SHAPE[2], SHAPE[1], SHAPE[0]], "out_dims_xyz": list(dims),
+                       "voxels_out_per_step_per_gpu": nvox_out, "l2": "ring of 3 input/output buffer pairs (~1 GB) "
+                       "larger than the 126 MB L2; each pair is also larger than L2", "parallelism": "one volume per GPU"},
+            "clocks": clocks,
+            "e2e": {"value": world * nvox_out * Ke / e2e_s / 1e9, "unit": UNIT, "h2d_bytes_per_step": 2 * nvox_in,
+                    "d2h_bytes_per_step": 2 * nvox_out, "steps": Ke, "ms_per_step": 1e3 * e2e_s / Ke,
+                    "api": "mia_resample_rigid_host (pinned host in/out, H2D+kernel+D2H pipelined by z-slab)",
+                    "max_abs_diff_vs_device_path": check},
+            "gpu_launches": K,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_kind": peak_kind, "kernel": "resample_kernel<i16,i16,kNone,store>",
+                         "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms_avg": kavg * 1e3,
+                         "kernel_ms_min": min(kernel_ms)},
+        }
+        if world == 1 and not args.no_cpu:
+            nv, times, threads = cpu_reslice_runs(mov_h, A, dims, 3)
+            line["cpu_baseline"] = {"value": nv / statistics.median(times) / 1e9, "unit": UNIT, "cores": threads,
+                                    "kind": "port", "sample": "full %dx%dx%d output volume, median of 3 runs "
+                                    "(C/OpenMP restatement of vtkImageReslice, float64)" % dims}
+        else:
+            line["cpu_baseline"] = None
+        if world == 1 and not args.no_extra:
+            del movs, outs
+            torch.cuda.empty_cache()
+            try:
+                line["extra"] = extras(dev, torch, kernels, peak)
+            except Exception as exc:           # the headline must survive a failing secondary measurement
+                line["extra"] = {"error": repr(exc)}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

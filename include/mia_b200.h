@@ -1,0 +1,145 @@
+/*
+ * mia_b200 -- C ABI of the B200-native rigid resample + similarity-metric hot path.
+ *
+ * The reference (caleb-oconnor/MedicalImageAnalysis v2.1.92) has NO FFI layer: it is pure Python over
+ * the VTK / SimpleITK wheels.  Each entry point below names the reference call site whose native
+ * arithmetic it replaces (paths relative to the reference checkout); INTEGRATION.md shows the ctypes
+ * stub a maintainer would drop into those sites.
+ *
+ * Conventions
+ *   - return 0 on success, negative on error; message via mia_last_error() (thread-local).
+ *   - volumes are dense, C-order [z][y][x] (Image.array layout, read/dicom.py:530-534); dims arrays are
+ *     (x, y, z) counts.  d_* pointers are DEVICE pointers owned by the caller; the library never allocates
+ *     or frees device memory on the d_* entry points (workspaces are caller supplied).
+ *   - A is the row-major 3x4 matrix "output voxel index (i,j,k,1) -> continuous moving index (x,y,z)",
+ *     float64, built on the host from spacing/origin/direction and the 4x4 rigid matrix.
+ *   - every d_* call is asynchronous on `stream` (a cudaStream_t passed as void*); no implicit sync.
+ *   - plain pointers and sizes only: no torch / CUDA types in the signatures.
+ */
+#ifndef MIA_B200_H
+#define MIA_B200_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MIA_B200_VERSION 100
+
+/* element types of Image.array on this path (read/dicom.py:530: int16; utils/creation.py:257: any) */
+#define MIA_I16 0
+#define MIA_F32 1
+
+/* border / rounding semantics */
+#define MIA_MODE_VTK 0 /* vtkImageReslice: inside [-0.5, N-0.5], int out = floor(v + 0.5)   */
+#define MIA_MODE_ITK 1 /* sitk.Resample:   inside [-0.5, N-0.5), int out = trunc(v)          */
+
+#define MIA_OK 0
+#define MIA_ERR_ARG (-1)
+#define MIA_ERR_DTYPE (-2)
+#define MIA_ERR_WORKSPACE (-3)
+#define MIA_ERR_CUDA (-4)
+#define MIA_ERR_UNSUPPORTED (-5)
+
+#define MIA_MAX_MATS 32  /* candidate matrices per batched metric launch */
+#define MIA_MAX_BINS 128 /* joint-histogram bins per axis (bins^2 uint32 counters live in shared memory) */
+
+int mia_version(void);
+const char *mia_last_error(void);
+
+/*
+ * Rigid trilinear resample of a device-resident moving volume onto an output lattice.
+ * Replaces the vtkImageReslice::Update() of Rigid.create_image (structure/rigid.py:685-693; twins
+ * structure/image.py:189-196, structure/dose.py:205-212) with mode = MIA_MODE_VTK, background = -3001,
+ * and sitk.Resample(mov, ref, T, sitkLinear, default, pixelID) of structure/deformable.py:579,788-795 /
+ * utils/deformable/simpleitk.py:81-94 with mode = MIA_MODE_ITK.
+ */
+int mia_resample_rigid(const void *d_mov, int mov_dtype, const int mdims[3], void *d_out, int out_dtype,
+                       const int odims[3], const double A[12], double background, int mode, void *stream);
+
+/*
+ * Same, HOST buffers in and out (the reference boundary: Image.array is a NumPy array and
+ * Display.compute_reslice adopts the output as one, structure/rigid.py:672,194-199).  The library
+ * stages through its own device buffers, pipelining H2D / kernel / D2H by z-slab on internal streams;
+ * synchronous on return.  device = CUDA ordinal.
+ */
+int mia_resample_rigid_host(const void *h_mov, int mov_dtype, const int mdims[3], void *h_out,
+                            int out_dtype, const int odims[3], const double A[12], double background,
+                            int mode, int device);
+
+/*
+ * Output lattice of vtkImageReslice with AutoCropOutputOn + identity output direction
+ * (structure/rigid.py:689-691): host-only helper, no GPU work.  M = 4x4 row-major fixed->moving physical,
+ * P2W_mov = 4x4 row-major moving index->physical.  extent_rule 0 = Round (VTK), 1 = ceil.
+ */
+int mia_autocrop_extent(const double M[16], const double P2W_mov[16], const int mdims[3],
+                        const double out_spacing[3], int extent_rule, int odims[3], double oorigin[3]);
+
+/*
+ * Exact axis permutation / flip copy: out = flip(transpose(in, perm), axes where flip[a] != 0), axes in
+ * [z, y, x] order (NumPy semantics).  Replaces the np.rot90 / np.flip / transpose views of the
+ * Feet-First-Supine normalisation (read/dicom.py:695-717, RTDOSE twin :2066-2088) that the reference
+ * materialises later with array.flatten() (structure/rigid.py:672).  Bit exact.  idims = (x, y, z) of `in`.
+ */
+int mia_permute_axes(const void *d_in, int dtype, const int idims[3], void *d_out, const int perm[3],
+                     const int flip[3], void *stream);
+
+/* Bytes of caller-supplied device workspace the two metric launches need (16-byte aligned base). */
+size_t mia_metric_workspace_bytes(const int odims[3], int n_mats, int bins);
+
+/*
+ * Fused resample + sum of squared differences over n_mats candidate matrices in ONE launch.
+ * For matrix m: d_ssd[m] = sum over fixed voxels whose sample is inside of (F - mov(A_m v))^2 with the
+ * UNROUNDED interpolated value, d_count[m] = number of inside voxels.  If d_out != NULL (n_mats must be 1)
+ * the resampled volume is also stored (background outside).  Matrices come from the host (A) or, when
+ * d_A != NULL, from device memory (for graph-captured optimiser loops).  No reference implementation
+ * exists (SetMetricAsMeanSquares is only named at utils/deformable/simpleitk.py:115): spec = SURVEY M1.
+ * The reduction is deterministic (fixed-order float64 second stage).
+ */
+int mia_resample_ssd(const void *d_mov, int mov_dtype, const int mdims[3], const void *d_fixed,
+                     int fixed_dtype, const int odims[3], void *d_out, int out_dtype, int n_mats,
+                     const double *A, const double *d_A, double background, int mode, double *d_ssd,
+                     unsigned long long *d_count, void *d_ws, size_t ws_bytes, void *stream);
+
+/*
+ * Fused resample + joint histogram: d_hist[m][bf][bm] (uint32, zeroed by the call) over inside voxels,
+ * bf = clamp(floor((F - fmin) * bins / (fmax - fmin)), 0, bins-1), bm likewise from the interpolated value.
+ * Spec = SURVEY M2 ("AdvancedMattesMutualInformation" + NumberOfHistogramBins are only named at
+ * utils/deformable/simpleitk.py:131,155-156).  Integer counts => bit-reproducible across shardings.
+ */
+int mia_resample_jointhist(const void *d_mov, int mov_dtype, const int mdims[3], const void *d_fixed,
+                           int fixed_dtype, const int odims[3], int n_mats, const double *A,
+                           const double *d_A, int mode, float fmin, float fmax, float mmin, float mmax,
+                           int bins, unsigned int *d_hist, unsigned long long *d_count, void *d_ws,
+                           size_t ws_bytes, void *stream);
+
+/* d_mi[m] = sum p_ij ln(p_ij / (p_i. p_.j)) in float64 from integer counts (natural log). */
+int mia_mi_from_hist(const unsigned int *d_hist, int bins, int n_mats, double *d_mi, void *stream);
+
+/*
+ * Device-side optimiser step (no host round trip): reads the 13 metric values of the current probe set,
+ * applies one regular-step gradient-descent update with central differences and step halving, and writes
+ * the next 13 candidate matrices to d_A.  See DESIGN.md "registration loop".  d_state is an opaque
+ * device block of mia_optimizer_state_bytes() bytes initialised by mia_optimizer_init.
+ */
+size_t mia_optimizer_state_bytes(void);
+int mia_optimizer_init(void *d_state, const double params0[6], const double center[3],
+                       const double P2W_fixed[16], const double W2P_mov[16], double rot_step_deg,
+                       double trans_step_mm, double min_step_scale, int maximize, double *d_A, void *stream);
+int mia_optimizer_step(void *d_state, const double *d_metric, const unsigned long long *d_count,
+                       int metric_is_ssd, double *d_A, void *stream);
+/* Copy the optimiser state back (synchronises `stream`).  Any output pointer may be NULL; hist_* hold
+ * min(iters, max_hist) entries: the centre cost, parameters [n][6] and step scale seen at each step. */
+int mia_optimizer_read(const void *d_state, double params[6], double *scale, int *iters, int *converged,
+                       int *n_reject, double *hist_cost, double *hist_params, double *hist_scale,
+                       int max_hist, void *stream);
+
+/* Page-locked host buffers for the *_host entry point (a NumPy array can wrap them). */
+void *mia_host_alloc(size_t bytes);
+int mia_host_free(void *p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MIA_B200_H */

@@ -1,0 +1,277 @@
+// C-ABI implementation of include/mia_b200.h.  Host dispatch only; kernels live in mia_kernels.cuh.
+#include "../../include/mia_b200.h"
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "mia_kernels.cuh"
+#include "mia_optimizer.cuh"
+
+using namespace mia;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                          \
+    do {                                                                                        \
+        cudaError_t e_ = (expr);                                                                \
+        if (e_ != cudaSuccess) return fail(MIA_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(e_)); \
+    } while (0)
+
+int sm_count()
+{
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (!cached[dev]) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
+bool dims_ok(const int d[3]) { return d && d[0] > 0 && d[1] > 0 && d[2] > 0; }
+bool dtype_ok(int t) { return t == MIA_I16 || t == MIA_F32; }
+size_t esize(int t) { return t == MIA_I16 ? 2 : 4; }
+
+constexpr int kMaxGridX = 148 * 16;   // upper bound of persistent grid.x used for workspace sizing
+
+struct WsLayout {
+    size_t off_A, off_ssd, off_cnt, off_ticket, total;
+};
+
+WsLayout ws_layout(int n_mats)
+{
+    WsLayout w;
+    size_t o = 0;
+    w.off_A = o;       o += sizeof(double) * 12 * MIA_MAX_MATS;
+    w.off_ssd = o;     o += sizeof(double) * (size_t)n_mats * kMaxGridX;
+    w.off_cnt = o;     o += sizeof(unsigned) * (size_t)n_mats * kMaxGridX;
+    w.off_ticket = o;  o += sizeof(unsigned) * MIA_MAX_MATS;
+    w.total = (o + 255) & ~(size_t)255;
+    return w;
+}
+
+void fill_common(KParams &p, const void *d_mov, const int mdims[3], const int odims[3])
+{
+    memset(&p, 0, sizeof p);
+    p.mov.p = d_mov;
+    p.mov.nx = mdims[0]; p.mov.ny = mdims[1]; p.mov.nz = mdims[2];
+    p.ox = odims[0]; p.oy = odims[1]; p.oz = odims[2];
+    p.ntx = (p.ox + (kV - 1) + kTileX - 1) / kTileX;   // rows are shifted by up to kV-1 for alignment
+    p.nty = (p.oy + kBlockY - 1) / kBlockY;
+    p.ntiles = (long long)p.ntx * p.nty * p.oz;
+}
+
+template <typename TM, typename TO>
+void launch_resample(const KParams &p, int mode, dim3 grid, cudaStream_t s)
+{
+    dim3 block(kBlockX, kBlockY);
+    if (mode == MIA_MODE_VTK)
+        resample_kernel<TM, int16_t, TO, kNone, true, true><<<grid, block, 0, s>>>(p);
+    else
+        resample_kernel<TM, int16_t, TO, kNone, true, false><<<grid, block, 0, s>>>(p);
+}
+
+template <typename TM, typename TF, int METRIC, bool STORE>
+void launch_metric(const KParams &p, int mode, dim3 grid, size_t smem, cudaStream_t s)
+{
+    dim3 block(kBlockX, kBlockY);
+    if (mode == MIA_MODE_VTK) {
+        auto k = resample_kernel<TM, TF, TM, METRIC, STORE, true>;
+        if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k<<<grid, block, smem, s>>>(p);
+    } else {
+        auto k = resample_kernel<TM, TF, TM, METRIC, STORE, false>;
+        if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k<<<grid, block, smem, s>>>(p);
+    }
+}
+
+template <int METRIC, bool STORE>
+void dispatch_metric(int mov_dtype, int fixed_dtype, const KParams &p, int mode, dim3 grid, size_t smem,
+                     cudaStream_t s)
+{
+    if (mov_dtype == MIA_I16 && fixed_dtype == MIA_I16)
+        launch_metric<int16_t, int16_t, METRIC, STORE>(p, mode, grid, smem, s);
+    else if (mov_dtype == MIA_I16 && fixed_dtype == MIA_F32)
+        launch_metric<int16_t, float, METRIC, STORE>(p, mode, grid, smem, s);
+    else if (mov_dtype == MIA_F32 && fixed_dtype == MIA_I16)
+        launch_metric<float, int16_t, METRIC, STORE>(p, mode, grid, smem, s);
+    else
+        launch_metric<float, float, METRIC, STORE>(p, mode, grid, smem, s);
+}
+
+}  // namespace
+
+extern "C" {
+
+int mia_version(void) { return MIA_B200_VERSION; }
+
+const char *mia_last_error(void) { return g_err.c_str(); }
+
+int mia_resample_rigid(const void *d_mov, int mov_dtype, const int mdims[3], void *d_out, int out_dtype,
+                       const int odims[3], const double A[12], double background, int mode, void *stream)
+{
+    if (!d_mov || !d_out || !A) return fail(MIA_ERR_ARG, "mia_resample_rigid: null pointer");
+    if (!dims_ok(mdims) || !dims_ok(odims)) return fail(MIA_ERR_ARG, "mia_resample_rigid: dims must be positive");
+    if (!dtype_ok(mov_dtype) || !dtype_ok(out_dtype))
+        return fail(MIA_ERR_DTYPE, "mia_resample_rigid: dtype must be MIA_I16 or MIA_F32");
+    if (mode != MIA_MODE_VTK && mode != MIA_MODE_ITK) return fail(MIA_ERR_ARG, "mia_resample_rigid: bad mode");
+    for (int i = 0; i < 12; ++i)
+        if (!std::isfinite(A[i])) return fail(MIA_ERR_ARG, "mia_resample_rigid: non-finite matrix");
+    KParams p;
+    fill_common(p, d_mov, mdims, odims);
+    p.out = d_out;
+    memcpy(p.A0.a, A, sizeof(double) * 12);
+    p.background = (float)background;
+    p.round_mode = mode == MIA_MODE_VTK ? 0 : 1;
+    if (p.ntiles > 0x7fffffffLL) return fail(MIA_ERR_UNSUPPORTED, "mia_resample_rigid: output too large");
+    dim3 grid((unsigned)p.ntiles, 1, 1);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (mov_dtype == MIA_I16 && out_dtype == MIA_I16) launch_resample<int16_t, int16_t>(p, mode, grid, s);
+    else if (mov_dtype == MIA_I16 && out_dtype == MIA_F32) launch_resample<int16_t, float>(p, mode, grid, s);
+    else if (mov_dtype == MIA_F32 && out_dtype == MIA_I16) launch_resample<float, int16_t>(p, mode, grid, s);
+    else launch_resample<float, float>(p, mode, grid, s);
+    CUDA_TRY(cudaGetLastError());
+    return MIA_OK;
+}
+
+size_t mia_metric_workspace_bytes(const int odims[3], int n_mats, int bins)
+{
+    (void)odims;
+    (void)bins;
+    if (n_mats < 1) n_mats = 1;
+    if (n_mats > MIA_MAX_MATS) n_mats = MIA_MAX_MATS;
+    return ws_layout(n_mats).total;
+}
+
+static int metric_common(KParams &p, const char *who, const void *d_mov, int mov_dtype, const int mdims[3],
+                         const void *d_fixed, int fixed_dtype, const int odims[3], int n_mats,
+                         const double *A, const double *d_A, int mode, void *d_ws, size_t ws_bytes,
+                         cudaStream_t s, WsLayout &w)
+{
+    if (!d_mov || !d_fixed || !d_ws) return fail(MIA_ERR_ARG, "%s: null pointer", who);
+    if (!A && !d_A) return fail(MIA_ERR_ARG, "%s: need A (host) or d_A (device)", who);
+    if (!dims_ok(mdims) || !dims_ok(odims)) return fail(MIA_ERR_ARG, "%s: dims must be positive", who);
+    if (!dtype_ok(mov_dtype) || !dtype_ok(fixed_dtype)) return fail(MIA_ERR_DTYPE, "%s: bad dtype", who);
+    if (n_mats < 1 || n_mats > MIA_MAX_MATS) return fail(MIA_ERR_ARG, "%s: n_mats must be 1..%d", who, MIA_MAX_MATS);
+    if (mode != MIA_MODE_VTK && mode != MIA_MODE_ITK) return fail(MIA_ERR_ARG, "%s: bad mode", who);
+    w = ws_layout(n_mats);
+    if (ws_bytes < w.total) return fail(MIA_ERR_WORKSPACE, "%s: workspace %zu < %zu bytes", who, ws_bytes, w.total);
+    if (((uintptr_t)d_ws & 15) != 0) return fail(MIA_ERR_WORKSPACE, "%s: workspace must be 16-byte aligned", who);
+    fill_common(p, d_mov, mdims, odims);
+    p.fixed = d_fixed;
+    char *ws = static_cast<char *>(d_ws);
+    p.ws_ssd = reinterpret_cast<double *>(ws + w.off_ssd);
+    p.ws_cnt = reinterpret_cast<unsigned *>(ws + w.off_cnt);
+    p.ws_ticket = reinterpret_cast<unsigned *>(ws + w.off_ticket);
+    p.round_mode = mode == MIA_MODE_VTK ? 0 : 1;
+    if (d_A) {
+        p.dA = d_A;
+    } else if (n_mats == 1) {
+        for (int i = 0; i < 12; ++i)
+            if (!std::isfinite(A[i])) return fail(MIA_ERR_ARG, "%s: non-finite matrix", who);
+        memcpy(p.A0.a, A, sizeof(double) * 12);
+        p.dA = nullptr;
+    } else {
+        for (int i = 0; i < 12 * n_mats; ++i)
+            if (!std::isfinite(A[i])) return fail(MIA_ERR_ARG, "%s: non-finite matrix", who);
+        CUDA_TRY(cudaMemcpyAsync(ws + w.off_A, A, sizeof(double) * 12 * n_mats, cudaMemcpyHostToDevice, s));
+        p.dA = reinterpret_cast<const double *>(ws + w.off_A);
+    }
+    CUDA_TRY(cudaMemsetAsync(p.ws_ticket, 0, sizeof(unsigned) * MIA_MAX_MATS, s));
+    return MIA_OK;
+}
+
+int mia_resample_ssd(const void *d_mov, int mov_dtype, const int mdims[3], const void *d_fixed,
+                     int fixed_dtype, const int odims[3], void *d_out, int out_dtype, int n_mats,
+                     const double *A, const double *d_A, double background, int mode, double *d_ssd,
+                     unsigned long long *d_count, void *d_ws, size_t ws_bytes, void *stream)
+{
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!d_ssd || !d_count) return fail(MIA_ERR_ARG, "mia_resample_ssd: null result pointer");
+    if (d_out && n_mats != 1) return fail(MIA_ERR_ARG, "mia_resample_ssd: storing needs n_mats == 1");
+    if (d_out && out_dtype != mov_dtype)
+        return fail(MIA_ERR_UNSUPPORTED, "mia_resample_ssd: stored output must have the moving dtype");
+    KParams p;
+    WsLayout w;
+    int rc = metric_common(p, "mia_resample_ssd", d_mov, mov_dtype, mdims, d_fixed, fixed_dtype, odims, n_mats,
+                           A, d_A, mode, d_ws, ws_bytes, s, w);
+    if (rc) return rc;
+    p.out = d_out;
+    p.background = (float)background;
+    p.d_ssd = d_ssd;
+    p.d_count = d_count;
+    long long gx = (long long)sm_count() * 8;
+    if (gx > p.ntiles) gx = p.ntiles;
+    if (gx > kMaxGridX) gx = kMaxGridX;
+    dim3 grid((unsigned)gx, (unsigned)n_mats, 1);
+    if (d_out) dispatch_metric<kSsd, true>(mov_dtype, fixed_dtype, p, mode, grid, 0, s);
+    else dispatch_metric<kSsd, false>(mov_dtype, fixed_dtype, p, mode, grid, 0, s);
+    CUDA_TRY(cudaGetLastError());
+    return MIA_OK;
+}
+
+int mia_resample_jointhist(const void *d_mov, int mov_dtype, const int mdims[3], const void *d_fixed,
+                           int fixed_dtype, const int odims[3], int n_mats, const double *A,
+                           const double *d_A, int mode, float fmin, float fmax, float mmin, float mmax,
+                           int bins, unsigned int *d_hist, unsigned long long *d_count, void *d_ws,
+                           size_t ws_bytes, void *stream)
+{
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!d_hist || !d_count) return fail(MIA_ERR_ARG, "mia_resample_jointhist: null result pointer");
+    if (bins < 2 || bins > MIA_MAX_BINS) return fail(MIA_ERR_ARG, "mia_resample_jointhist: bins must be 2..%d", MIA_MAX_BINS);
+    if (!(fmax > fmin) || !(mmax > mmin)) return fail(MIA_ERR_ARG, "mia_resample_jointhist: empty intensity range");
+    KParams p;
+    WsLayout w;
+    int rc = metric_common(p, "mia_resample_jointhist", d_mov, mov_dtype, mdims, d_fixed, fixed_dtype, odims,
+                           n_mats, A, d_A, mode, d_ws, ws_bytes, s, w);
+    if (rc) return rc;
+    p.d_hist = d_hist;
+    p.d_count = d_count;
+    p.bins = bins;
+    p.fmin = fmin; p.fscale = (float)bins / (fmax - fmin);
+    p.mmin = mmin; p.mscale = (float)bins / (mmax - mmin);
+    CUDA_TRY(cudaMemsetAsync(d_hist, 0, sizeof(unsigned) * (size_t)n_mats * bins * bins, s));
+    const size_t smem = sizeof(unsigned) * (size_t)bins * bins;
+    long long gx = (long long)sm_count() * (smem > 32 * 1024 ? 2 : 4);
+    if (gx > p.ntiles) gx = p.ntiles;
+    if (gx > kMaxGridX) gx = kMaxGridX;
+    dim3 grid((unsigned)gx, (unsigned)n_mats, 1);
+    dispatch_metric<kHist, false>(mov_dtype, fixed_dtype, p, mode, grid, smem, s);
+    CUDA_TRY(cudaGetLastError());
+    return MIA_OK;
+}
+
+int mia_mi_from_hist(const unsigned int *d_hist, int bins, int n_mats, double *d_mi, void *stream)
+{
+    if (!d_hist || !d_mi) return fail(MIA_ERR_ARG, "mia_mi_from_hist: null pointer");
+    if (bins < 2 || bins > MIA_MAX_BINS || n_mats < 1) return fail(MIA_ERR_ARG, "mia_mi_from_hist: bad bins / n_mats");
+    const size_t smem = sizeof(double) * (2 * (size_t)bins + 256);
+    mi_kernel<<<n_mats, 256, smem, (cudaStream_t)stream>>>(d_hist, bins, d_mi);
+    CUDA_TRY(cudaGetLastError());
+    return MIA_OK;
+}
+
+}  // extern "C"
+
+#include "mia_host_api.inl"

@@ -1,0 +1,137 @@
+// Device-side building blocks of the rigid resample + metric kernels (sm_100a).
+//
+// Data layout in HBM: volumes are dense [z][y][x]; int16 (CT/MR/PT as the reference reader produces,
+// read/dicom.py:530) or float32.  One thread owns V consecutive output voxels along x so the output
+// store (and the fixed-image load of the fused metrics) is one 8/16-byte vector access, warps cover
+// 32*V contiguous output voxels => fully coalesced 256/512-byte row segments.
+//
+// Coordinates: the first voxel of a thread is mapped through A in float64 (12 DFMA per V voxels),
+// split into an integer base and a float32 fraction; the remaining V-1 voxels advance by the float32
+// x-column of A from that fraction.  All float32 coordinates are therefore LOCAL (|c| < V + 1), which
+// keeps the weight error near 1e-7 voxel regardless of volume size (a global float32 coordinate at
+// x = 1000 would carry 6e-5) and makes the +-0.5 border test agree with the float64 oracle.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace mia {
+
+constexpr int kV = 4;          // output voxels per thread along x
+constexpr int kBlockX = 32;    // threads along x  -> 128 voxels
+constexpr int kBlockY = 8;     // rows per block
+constexpr int kThreads = kBlockX * kBlockY;
+constexpr int kTileX = kBlockX * kV;
+
+struct VolView {
+    const void *p;
+    int nx, ny, nz;
+};
+
+struct Mat34 {
+    double a[12];
+};
+
+template <typename T>
+__device__ __forceinline__ float ld_tap(const T *__restrict__ p, size_t i)
+{
+    return static_cast<float>(__ldg(p + i));
+}
+
+__device__ __forceinline__ int clampi(int v, int lo, int hi) { return min(max(v, lo), hi); }
+
+// Per-thread sampling context: integer base of the first voxel and the float32 increments.
+struct RowCtx {
+    int bx, by, bz;        // floor of the first voxel's continuous index
+    float fx, fy, fz;      // its fractional part (exact to 2^-25)
+    float ax, ay, az;      // d(c)/d(i): x column of A in float32
+    float lox, loy, loz;   // -0.5 - base   (exact)
+    float hix, hiy, hiz;   // N - 0.5 - base (exact)
+};
+
+__device__ __forceinline__ RowCtx make_row_ctx(const double *__restrict__ A, int i, int j, int k,
+                                               int nx, int ny, int nz)
+{
+    RowCtx r;
+    // association order of vtkImageResliceExecute: origin + k*z + j*y + i*x
+    double cx = ((A[3] + (double)k * A[2]) + (double)j * A[1]) + (double)i * A[0];
+    double cy = ((A[7] + (double)k * A[6]) + (double)j * A[5]) + (double)i * A[4];
+    double cz = ((A[11] + (double)k * A[10]) + (double)j * A[9]) + (double)i * A[8];
+    // clamp far-away coordinates so the int conversion cannot overflow; anything beyond is outside anyway
+    const double big = 1.0e9;
+    cx = fmin(fmax(cx, -big), big);
+    cy = fmin(fmax(cy, -big), big);
+    cz = fmin(fmax(cz, -big), big);
+    double flx = floor(cx), fly = floor(cy), flz = floor(cz);
+    r.bx = (int)flx; r.by = (int)fly; r.bz = (int)flz;
+    r.fx = (float)(cx - flx); r.fy = (float)(cy - fly); r.fz = (float)(cz - flz);
+    r.ax = (float)A[0]; r.ay = (float)A[4]; r.az = (float)A[8];
+    r.lox = -0.5f - (float)r.bx; r.loy = -0.5f - (float)r.by; r.loz = -0.5f - (float)r.bz;
+    r.hix = (float)nx - 0.5f - (float)r.bx;
+    r.hiy = (float)ny - 0.5f - (float)r.by;
+    r.hiz = (float)nz - 0.5f - (float)r.bz;
+    return r;
+}
+
+// Sample voxel number v (0..V-1) of the thread.  Returns inside flag; value in `val` (unrounded float32).
+template <typename TM, bool CLOSED>
+__device__ __forceinline__ bool sample_voxel(const TM *__restrict__ mov, int nx, int ny, int nz,
+                                             const RowCtx &r, int v, float &val)
+{
+    const float lx = fmaf((float)v, r.ax, r.fx);
+    const float ly = fmaf((float)v, r.ay, r.fy);
+    const float lz = fmaf((float)v, r.az, r.fz);
+    bool in = (lx >= r.lox) & (ly >= r.loy) & (lz >= r.loz);
+    if (CLOSED)
+        in &= (lx <= r.hix) & (ly <= r.hiy) & (lz <= r.hiz);
+    else
+        in &= (lx < r.hix) & (ly < r.hiy) & (lz < r.hiz);
+    if (!in) return false;
+    const float flx = floorf(lx), fly = floorf(ly), flz = floorf(lz);
+    const float wx = lx - flx, wy = ly - fly, wz = lz - flz;
+    const int ix = r.bx + (int)flx, iy = r.by + (int)fly, iz = r.bz + (int)flz;
+    const int x0 = clampi(ix, 0, nx - 1), x1 = clampi(ix + 1, 0, nx - 1);
+    const int y0 = clampi(iy, 0, ny - 1), y1 = clampi(iy + 1, 0, ny - 1);
+    const int z0 = clampi(iz, 0, nz - 1), z1 = clampi(iz + 1, 0, nz - 1);
+    const size_t r00 = ((size_t)z0 * ny + y0) * nx, r10 = ((size_t)z0 * ny + y1) * nx;
+    const size_t r01 = ((size_t)z1 * ny + y0) * nx, r11 = ((size_t)z1 * ny + y1) * nx;
+    const float v000 = ld_tap(mov, r00 + x0), v100 = ld_tap(mov, r00 + x1);
+    const float v010 = ld_tap(mov, r10 + x0), v110 = ld_tap(mov, r10 + x1);
+    const float v001 = ld_tap(mov, r01 + x0), v101 = ld_tap(mov, r01 + x1);
+    const float v011 = ld_tap(mov, r11 + x0), v111 = ld_tap(mov, r11 + x1);
+    const float vx00 = fmaf(wx, v100 - v000, v000);
+    const float vx10 = fmaf(wx, v110 - v010, v010);
+    const float vx01 = fmaf(wx, v101 - v001, v001);
+    const float vx11 = fmaf(wx, v111 - v011, v011);
+    const float vxx0 = fmaf(wy, vx10 - vx00, vx00);
+    const float vxx1 = fmaf(wy, vx11 - vx01, vx01);
+    val = fmaf(wz, vxx1 - vxx0, vxx0);
+    return true;
+}
+
+// float -> output element.  ROUND: 0 = floor(v + 0.5) (VTK), 1 = trunc (ITK); clamp to the type range first.
+template <typename TO>
+__device__ __forceinline__ TO to_out(float v, int round_mode);
+
+template <>
+__device__ __forceinline__ float to_out<float>(float v, int) { return v; }
+
+template <>
+__device__ __forceinline__ int16_t to_out<int16_t>(float v, int round_mode)
+{
+    v = fminf(fmaxf(v, -32768.0f), 32767.0f);
+    return (int16_t)(round_mode == 0 ? floorf(v + 0.5f) : truncf(v));
+}
+
+__device__ __forceinline__ float warp_sum(float v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__device__ __forceinline__ unsigned warp_sum_u(unsigned v)
+{
+    return __reduce_add_sync(0xffffffffu, v);
+}
+
+}  // namespace mia

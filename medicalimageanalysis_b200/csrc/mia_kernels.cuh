@@ -1,0 +1,335 @@
+// Kernels of the rigid resample + metric hot path (sm_100a).  See DESIGN.md for the roofline of each.
+#pragma once
+#include "mia_device.cuh"
+
+namespace mia {
+
+enum Metric { kNone = 0, kSsd = 1, kHist = 2 };
+
+struct KParams {
+    VolView mov;                 // moving volume
+    const void *fixed;           // fixed volume on the output lattice (metrics) or nullptr
+    void *out;                   // resampled output or nullptr
+    int ox, oy, oz;              // output lattice
+    int ntx, nty;                // tiles along x / y
+    long long ntiles;            // ntx * nty * oz
+    Mat34 A0;                    // matrix 0 by value (host-matrix path, n_mats == 1)
+    const double *dA;            // [n_mats][12] device matrices, or nullptr -> A0
+    float background;
+    int round_mode;              // 0 half-up, 1 trunc
+    // metric outputs
+    double *ws_ssd;              // [n_mats][gridDim.x] block partials
+    unsigned *ws_cnt;            // [n_mats][gridDim.x]
+    unsigned *ws_ticket;         // [n_mats]
+    double *d_ssd;               // [n_mats]
+    unsigned long long *d_count; // [n_mats]
+    unsigned *d_hist;            // [n_mats][bins][bins]
+    float fmin, fscale, mmin, mscale;
+    int bins;
+};
+
+template <typename T, int N>
+struct alignas(sizeof(T) * N) Vec {
+    T v[N];
+};
+
+__device__ __forceinline__ int bin_of(float v, float vmin, float scale, int bins)
+{
+    float b = floorf((v - vmin) * scale);
+    b = fminf(fmaxf(b, 0.0f), (float)(bins - 1));   // NaN -> 0 via fmaxf
+    return (int)b;
+}
+
+// One launch does everything: grid.x blocks stride over the (x-tile, y-tile, z) tiles of the output
+// lattice, grid.y = candidate matrix.  METRIC selects the fused reduction.
+template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool CLOSED>
+__global__ void __launch_bounds__(kThreads) resample_kernel(const KParams p)
+{
+    extern __shared__ unsigned s_hist[];        // METRIC == kHist: bins*bins counters
+    __shared__ double s_red[kThreads / 32];
+    __shared__ unsigned s_redc[kThreads / 32];
+    __shared__ bool s_last;
+
+    const int m = blockIdx.y;
+    const double *A = p.dA ? p.dA + 12 * m : p.A0.a;
+    const TM *mov = static_cast<const TM *>(p.mov.p);
+    const TF *fixed = static_cast<const TF *>(p.fixed);
+    TO *out = static_cast<TO *>(p.out);
+    const int nx = p.mov.nx, ny = p.mov.ny, nz = p.mov.nz;
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    const int tid = ty * kBlockX + tx;
+
+    if (METRIC == kHist) {
+        for (int b = tid; b < p.bins * p.bins; b += kThreads) s_hist[b] = 0u;
+        __syncthreads();
+    }
+
+    double acc = 0.0;
+    unsigned cnt = 0;
+
+    for (long long tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+        const int tix = (int)(tile % p.ntx);
+        const long long t2 = tile / p.ntx;
+        const int tiy = (int)(t2 % p.nty);
+        const int k = (int)(t2 / p.nty);
+        const int j = tiy * kBlockY + ty;
+        if (j >= p.oy) continue;
+        const size_t rowbase = ((size_t)k * p.oy + j) * p.ox;
+        // Shift the 4-voxel chunks of this row so that every full chunk is a naturally aligned vector:
+        // rows of an auto-cropped lattice have arbitrary length, so the misalignment differs per row.
+        unsigned mis;
+        if (STORE) mis = (unsigned)(reinterpret_cast<uintptr_t>(out + rowbase) / sizeof(TO)) & (kV - 1);
+        else mis = (unsigned)(reinterpret_cast<uintptr_t>(fixed + rowbase) / sizeof(TF)) & (kV - 1);
+        const int i0 = tix * kTileX + tx * kV - (int)mis;
+        if (i0 >= p.ox || i0 + kV <= 0) continue;
+        const bool full = (i0 >= 0) && (i0 + kV <= p.ox);
+        const size_t row = rowbase + i0;          // may point before the row when i0 < 0: only used when full
+
+        const RowCtx r = make_row_ctx(A, i0, j, k, nx, ny, nz);
+
+        float fv[kV];
+        if (METRIC != kNone) {
+            const bool fvec = full && ((reinterpret_cast<uintptr_t>(fixed + row) & (sizeof(TF) * kV - 1)) == 0);
+            if (fvec) {
+                const Vec<TF, kV> f = *reinterpret_cast<const Vec<TF, kV> *>(fixed + row);
+#pragma unroll
+                for (int v = 0; v < kV; ++v) fv[v] = (float)f.v[v];
+            } else {
+#pragma unroll
+                for (int v = 0; v < kV; ++v)
+                    fv[v] = (i0 + v >= 0 && i0 + v < p.ox) ? (float)fixed[rowbase + i0 + v] : 0.0f;
+            }
+        }
+
+        Vec<TO, kV> o;
+        float part = 0.0f;
+#pragma unroll
+        for (int v = 0; v < kV; ++v) {
+            float val;
+            const bool live = full || (i0 + v >= 0 && i0 + v < p.ox);
+            const bool in = live && sample_voxel<TM, CLOSED>(mov, nx, ny, nz, r, v, val);
+            if (STORE) o.v[v] = in ? to_out<TO>(val, p.round_mode) : to_out<TO>(p.background, p.round_mode);
+            if (METRIC == kSsd && in) {
+                const float d = fv[v] - val;
+                part = fmaf(d, d, part);
+                ++cnt;
+            }
+            if (METRIC == kHist && in) {
+                const int bf = bin_of(fv[v], p.fmin, p.fscale, p.bins);
+                const int bm = bin_of(val, p.mmin, p.mscale, p.bins);
+                atomicAdd(&s_hist[bf * p.bins + bm], 1u);
+                ++cnt;
+            }
+        }
+        if (METRIC == kSsd) acc += (double)part;
+        if (STORE) {
+            if (full) {
+                *reinterpret_cast<Vec<TO, kV> *>(out + row) = o;
+            } else {
+#pragma unroll
+                for (int v = 0; v < kV; ++v)
+                    if (i0 + v >= 0 && i0 + v < p.ox) out[rowbase + i0 + v] = o.v[v];
+            }
+        }
+    }
+
+    if (METRIC == kNone) return;
+
+    // ---- block reduction (fixed order => deterministic for a given grid) ----
+    const int lane = tid & 31, warp = tid >> 5;
+    if (METRIC == kSsd) {
+        // double warp reduction through two 32-bit shuffles per step
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    }
+    cnt = warp_sum_u(cnt);
+    if (lane == 0) {
+        s_red[warp] = acc;
+        s_redc[warp] = cnt;
+    }
+    __syncthreads();
+
+    if (METRIC == kHist) {
+        // flush the privatised histogram; integer adds commute, so order does not matter
+        unsigned *gh = p.d_hist + (size_t)m * p.bins * p.bins;
+        for (int b = tid; b < p.bins * p.bins; b += kThreads) {
+            const unsigned c = s_hist[b];
+            if (c) atomicAdd(gh + b, c);
+        }
+    }
+
+    if (tid == 0) {
+        double s = 0.0;
+        unsigned c = 0;
+        for (int w = 0; w < kThreads / 32; ++w) {
+            s += s_red[w];
+            c += s_redc[w];
+        }
+        p.ws_ssd[(size_t)m * gridDim.x + blockIdx.x] = s;
+        p.ws_cnt[(size_t)m * gridDim.x + blockIdx.x] = c;
+        __threadfence();
+        const unsigned t = atomicAdd(p.ws_ticket + m, 1u);
+        s_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+
+    // last block of this matrix: fixed-order second stage over all block partials
+    __threadfence();
+    double s = 0.0;
+    unsigned long long c = 0;
+    for (unsigned b = tid; b < gridDim.x; b += kThreads) {
+        s += __ldcg(p.ws_ssd + (size_t)m * gridDim.x + b);
+        c += __ldcg(p.ws_cnt + (size_t)m * gridDim.x + b);
+    }
+    __shared__ double s_fin[kThreads];
+    __shared__ unsigned long long s_finc[kThreads];
+    s_fin[tid] = s;
+    s_finc[tid] = c;
+    __syncthreads();
+    for (int o = kThreads / 2; o > 0; o >>= 1) {
+        if (tid < o) {
+            s_fin[tid] += s_fin[tid + o];
+            s_finc[tid] += s_finc[tid + o];
+        }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        if (METRIC == kSsd) p.d_ssd[m] = s_fin[0];
+        p.d_count[m] = s_finc[0];
+        p.ws_ticket[m] = 0u;     // self-reset: the workspace is reusable without a memset
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// MI from an integer joint histogram: one block per matrix, float64, fixed-order tree reductions.
+__global__ void __launch_bounds__(256) mi_kernel(const unsigned *__restrict__ hist, int bins, double *mi)
+{
+    extern __shared__ double s_buf[];        // [bins] row sums, [bins] col sums, [256] scratch
+    double *rowsum = s_buf, *colsum = s_buf + bins, *red = s_buf + 2 * bins;
+    const unsigned *h = hist + (size_t)blockIdx.x * bins * bins;
+    const int tid = threadIdx.x;
+    for (int b = tid; b < bins; b += 256) {
+        double rs = 0.0, cs = 0.0;
+        for (int q = 0; q < bins; ++q) {
+            rs += (double)h[b * bins + q];
+            cs += (double)h[q * bins + b];
+        }
+        rowsum[b] = rs;
+        colsum[b] = cs;
+    }
+    __syncthreads();
+    double part = 0.0;
+    for (int b = tid; b < bins; b += 256) part += rowsum[b];
+    red[tid] = part;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (tid < o) red[tid] += red[tid + o];
+        __syncthreads();
+    }
+    const double n = red[0];
+    __syncthreads();
+    part = 0.0;
+    if (n > 0.0) {
+        for (int e = tid; e < bins * bins; e += 256) {
+            const unsigned c = h[e];
+            if (c) {
+                const double hc = (double)c;
+                part += (hc / n) * log(hc * n / (rowsum[e / bins] * colsum[e % bins]));
+            }
+        }
+    }
+    red[tid] = part;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (tid < o) red[tid] += red[tid + o];
+        __syncthreads();
+    }
+    if (tid == 0) mi[blockIdx.x] = red[0];
+}
+
+// ---------------------------------------------------------------------------------------------
+// Exact axis permutation / flip (Feet-First-Supine normalisation).  Axes in [z,y,x] order.
+struct PermParams {
+    const void *in;
+    void *out;
+    int idim[3];     // input dims  [z,y,x]
+    int odim[3];     // output dims [z,y,x]
+    int perm[3];     // output axis a reads input axis perm[a]
+    int flip[3];     // output axis a reversed
+};
+
+// Path A: input x stays the fastest output axis (possibly reversed): row copies, coalesced both sides.
+template <typename T>
+__global__ void __launch_bounds__(256) permute_rows_kernel(const PermParams p)
+{
+    const T *in = static_cast<const T *>(p.in);
+    T *out = static_cast<T *>(p.out);
+    const int ox = p.odim[2];
+    const long long rows = (long long)p.odim[0] * p.odim[1];
+    const int rows_per_block = blockDim.y;
+    for (long long r = (long long)blockIdx.x * rows_per_block + threadIdx.y; r < rows;
+         r += (long long)gridDim.x * rows_per_block) {
+        const int o0 = (int)(r / p.odim[1]), o1 = (int)(r % p.odim[1]);
+        int idx[3];
+        idx[p.perm[0]] = p.flip[0] ? p.odim[0] - 1 - o0 : o0;
+        idx[p.perm[1]] = p.flip[1] ? p.odim[1] - 1 - o1 : o1;
+        const T *src = in + ((size_t)idx[0] * p.idim[1] + idx[1]) * p.idim[2];
+        T *dst = out + (size_t)r * ox;
+        if (p.flip[2]) {
+            for (int x = threadIdx.x; x < ox; x += blockDim.x) dst[x] = __ldg(src + (ox - 1 - x));
+        } else {
+            for (int x = threadIdx.x; x < ox; x += blockDim.x) dst[x] = __ldg(src + x);
+        }
+    }
+}
+
+// Path B: input x becomes output axis pa != 2 -> 32x32 (x4 rows per thread) transpose through shared memory.
+// The tile plane is (input x) x (input axis q = perm[2] that becomes output x).
+template <typename T>
+__global__ void __launch_bounds__(256) permute_transpose_kernel(const PermParams p, int pa, int pc)
+{
+    // pa: output axis fed by input x; pc: the remaining output axis (batch)
+    __shared__ T tile[32][33];
+    const T *in = static_cast<const T *>(p.in);
+    T *out = static_cast<T *>(p.out);
+    const int q = p.perm[2];                 // input axis that becomes output x
+    const int c_in = p.perm[pc];             // input axis of the batch dimension
+    const int nxin = p.idim[2];              // length along input x   (= odim[pa])
+    const int nq = p.idim[q];                // length along input q   (= odim[2])
+    const int tiles_x = (nxin + 31) / 32, tiles_q = (nq + 31) / 32;
+    const long long ntiles = (long long)tiles_x * tiles_q * p.odim[pc];
+    for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const int tx0 = (int)(t % tiles_x) * 32;
+        const long long t2 = t / tiles_x;
+        const int tq0 = (int)(t2 % tiles_q) * 32;
+        const int oc = (int)(t2 / tiles_q);  // output index along pc
+        const int ic = p.flip[pc] ? p.odim[pc] - 1 - oc : oc;
+        // load: threads sweep input x (fast), rows along input q
+        for (int rr = threadIdx.y; rr < 32; rr += 8) {
+            const int xi = tx0 + threadIdx.x, qi = tq0 + rr;
+            if (xi < nxin && qi < nq) {
+                int idx[3];
+                idx[2] = xi;
+                idx[q] = qi;
+                idx[c_in] = ic;
+                tile[rr][threadIdx.x] = __ldg(in + ((size_t)idx[0] * p.idim[1] + idx[1]) * p.idim[2] + idx[2]);
+            }
+        }
+        __syncthreads();
+        // store: threads sweep output x (input q), rows along output pa (input x)
+        for (int rr = threadIdx.y; rr < 32; rr += 8) {
+            const int qi = tq0 + threadIdx.x, xi = tx0 + rr;
+            if (xi < nxin && qi < nq) {
+                int o[3];
+                o[2] = p.flip[2] ? nq - 1 - qi : qi;
+                o[pa] = p.flip[pa] ? nxin - 1 - xi : xi;
+                o[pc] = oc;
+                out[((size_t)o[0] * p.odim[1] + o[1]) * p.odim[2] + o[2]] = tile[threadIdx.x][rr];
+            }
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace mia

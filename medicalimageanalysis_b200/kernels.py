@@ -1,0 +1,205 @@
+"""Thin tensor-level wrappers over the C ABI.  Tensors are storage; all arithmetic is in libmia_b200.so.
+
+Every function takes CUDA ``torch.Tensor`` volumes laid out ``[z, y, x]`` contiguous (the ``Image.array``
+layout of the reference, ``read/dicom.py:530-534``) and 3x4 index matrices (see ``geometry.py``), launches
+on the current torch stream and returns device tensors without synchronising.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import MIA_F32, MIA_I16, MIA_MODE_ITK, MIA_MODE_VTK, check, darr, i3
+
+_DT = {torch.int16: MIA_I16, torch.float32: MIA_F32}
+_NP_DT = {np.dtype(np.int16): MIA_I16, np.dtype(np.float32): MIA_F32}
+_MODE = {"vtk": MIA_MODE_VTK, "itk": MIA_MODE_ITK}
+
+FFS_PERMUTATIONS = {
+    # case -> (perm, flip) in [z, y, x] axes: out = flip(transpose(in, perm), flip axes)
+    "axial_k1": ((0, 2, 1), (0, 1, 0)),   # np.rot90(a, 1, (1, 2))  read/dicom.py:697
+    "axial_k3": ((0, 2, 1), (0, 0, 1)),   # np.rot90(a, 3, (1, 2))  read/dicom.py:699
+    "axial_k2": ((0, 1, 2), (0, 1, 1)),   # np.rot90(a, 2, (1, 2))  read/dicom.py:701
+    "coronal":  ((1, 0, 2), (1, 0, 0)),   # np.rot90(a, 1, (0, 1))  read/dicom.py:709
+    "sagittal": ((1, 2, 0), (1, 0, 1)),   # flip(rot90(a,1,(0,1)).transpose(0,2,1), 2)  read/dicom.py:717
+}
+
+
+def _vol(t, name):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise TypeError("%s must be a CUDA torch.Tensor (there is no CPU path)" % name)
+    if t.dim() != 3:
+        raise ValueError("%s must be 3-D [z, y, x]" % name)
+    if t.dtype not in _DT:
+        raise TypeError("%s dtype must be int16 or float32, got %s" % (name, t.dtype))
+    if not t.is_contiguous():
+        t = t.contiguous()
+    return t
+
+
+def _dims(t):
+    return i3((t.shape[2], t.shape[1], t.shape[0]))
+
+
+def _stream(t):
+    return ctypes.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
+
+
+def _mats(A):
+    A = np.ascontiguousarray(np.asarray(A, dtype=np.float64))
+    if A.ndim == 2:
+        A = A[None]
+    if A.shape[1:] != (3, 4):
+        raise ValueError("index matrices must be [n, 3, 4] or [3, 4]")
+    return A
+
+
+def resample(mov, A, out_shape, background=-3001.0, mode="vtk", out_dtype=None, out=None):
+    """Trilinear resample of ``mov`` onto an ``out_shape`` ([z,y,x]) lattice through the 3x4 ``A``."""
+    lib = _lib.load()
+    mov = _vol(mov, "mov")
+    out_dtype = out_dtype or mov.dtype
+    if out is None:
+        out = torch.empty(tuple(int(s) for s in out_shape), dtype=out_dtype, device=mov.device)
+    else:
+        out = _vol(out, "out")
+    A = _mats(A)
+    if A.shape[0] != 1:
+        raise ValueError("resample takes exactly one matrix")
+    with torch.cuda.device(mov.device):
+        check(lib.mia_resample_rigid(mov.data_ptr(), _DT[mov.dtype], _dims(mov), out.data_ptr(), _DT[out.dtype],
+                                     _dims(out), darr(A.ravel()), float(background), _MODE[mode], _stream(mov)))
+    return out
+
+
+def resample_host(mov, A, out_shape, background=-3001.0, mode="vtk", out_dtype=None, out=None, device=0):
+    """NumPy in, NumPy out through ``mia_resample_rigid_host`` (H2D / kernel / D2H pipelined by z-slab)."""
+    lib = _lib.load()
+    mov = np.ascontiguousarray(mov)
+    if mov.dtype not in _NP_DT or mov.ndim != 3:
+        raise TypeError("mov must be a 3-D int16 or float32 array")
+    out_dtype = np.dtype(out_dtype or mov.dtype)
+    if out is None:
+        out = np.empty(tuple(int(s) for s in out_shape), dtype=out_dtype)
+    A = _mats(A)
+    md = i3((mov.shape[2], mov.shape[1], mov.shape[0]))
+    od = i3((out.shape[2], out.shape[1], out.shape[0]))
+    check(lib.mia_resample_rigid_host(mov.ctypes.data, _NP_DT[mov.dtype], md, out.ctypes.data, _NP_DT[out.dtype], od,
+                                      darr(A.ravel()), float(background), _MODE[mode], int(device)))
+    return out
+
+
+def pinned_empty(shape, dtype):
+    """A NumPy array over page-locked memory from ``mia_host_alloc`` (freed when the array dies)."""
+    lib = _lib.load()
+    dtype = np.dtype(dtype)
+    n = int(np.prod(shape)) * dtype.itemsize
+    p = lib.mia_host_alloc(n)
+    if not p:
+        raise _lib.MiaError(-4, (lib.mia_last_error() or b"").decode())
+    buf = (ctypes.c_char * max(n, 1)).from_address(p)
+    arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+    import weakref
+    weakref.finalize(buf, lib.mia_host_free, p)
+    return arr
+
+
+def permute_axes(vol, perm, flip, out=None):
+    """Exact ``np.flip(np.transpose(vol, perm), flipped axes)`` on the device."""
+    lib = _lib.load()
+    vol = _vol(vol, "vol")
+    oshape = tuple(vol.shape[p] for p in perm)
+    if out is None:
+        out = torch.empty(oshape, dtype=vol.dtype, device=vol.device)
+    with torch.cuda.device(vol.device):
+        check(lib.mia_permute_axes(vol.data_ptr(), _DT[vol.dtype], _dims(vol), out.data_ptr(), i3(perm), i3(flip),
+                                   _stream(vol)))
+    return out
+
+
+class MetricWorkspace:
+    """Caller-owned device scratch + result buffers for the fused metric launches (reused across calls)."""
+
+    def __init__(self, device, n_mats=1, bins=64):
+        lib = _lib.load()
+        self.device = torch.device(device)
+        self.n_mats, self.bins = int(n_mats), int(bins)
+        nbytes = int(lib.mia_metric_workspace_bytes(i3((1, 1, 1)), self.n_mats, self.bins))
+        self.ws = torch.zeros(nbytes, dtype=torch.uint8, device=self.device)
+        self.ssd = torch.zeros(self.n_mats, dtype=torch.float64, device=self.device)
+        self.count = torch.zeros(self.n_mats, dtype=torch.int64, device=self.device)
+        self.hist = torch.zeros((self.n_mats, self.bins, self.bins), dtype=torch.int32, device=self.device)
+        self.mi = torch.zeros(self.n_mats, dtype=torch.float64, device=self.device)
+
+
+def _A_args(A, d_A, n_expected=None):
+    if d_A is not None:
+        if d_A.dtype != torch.float64 or not d_A.is_cuda or not d_A.is_contiguous():
+            raise TypeError("d_A must be a contiguous CUDA float64 tensor [n, 3, 4]")
+        n = d_A.numel() // 12
+        return n, None, ctypes.c_void_p(d_A.data_ptr())
+    A = _mats(A)
+    return A.shape[0], darr(A.ravel()), None
+
+
+def resample_ssd(fixed, mov, A=None, d_A=None, mode="itk", ws=None, out=None, background=0.0):
+    """Fused resample + SSD for n candidate matrices in one launch.  Returns (ssd[n] f64, count[n] i64)
+    device tensors (views into ``ws``).  ``out`` (n == 1) also stores the resampled volume."""
+    lib = _lib.load()
+    fixed, mov = _vol(fixed, "fixed"), _vol(mov, "mov")
+    n, Ah, Ad = _A_args(A, d_A)
+    if ws is None or ws.n_mats < n:
+        ws = MetricWorkspace(mov.device, n_mats=n)
+    if out is not None:
+        out = _vol(out, "out")
+    with torch.cuda.device(mov.device):
+        check(lib.mia_resample_ssd(mov.data_ptr(), _DT[mov.dtype], _dims(mov), fixed.data_ptr(), _DT[fixed.dtype],
+                                   _dims(fixed), out.data_ptr() if out is not None else None,
+                                   _DT[out.dtype] if out is not None else _DT[mov.dtype], n, Ah, Ad,
+                                   float(background), _MODE[mode], ws.ssd.data_ptr(), ws.count.data_ptr(),
+                                   ws.ws.data_ptr(), ws.ws.numel(), _stream(mov)))
+    return ws.ssd[:n], ws.count[:n]
+
+
+def resample_jointhist(fixed, mov, frange, mrange, bins=64, A=None, d_A=None, mode="itk", ws=None):
+    """Fused resample + joint histogram.  Returns (hist[n, bins, bins] int32, count[n] i64) device tensors."""
+    lib = _lib.load()
+    fixed, mov = _vol(fixed, "fixed"), _vol(mov, "mov")
+    n, Ah, Ad = _A_args(A, d_A)
+    if ws is None or ws.n_mats < n or ws.bins != bins:
+        ws = MetricWorkspace(mov.device, n_mats=n, bins=bins)
+    with torch.cuda.device(mov.device):
+        check(lib.mia_resample_jointhist(mov.data_ptr(), _DT[mov.dtype], _dims(mov), fixed.data_ptr(),
+                                         _DT[fixed.dtype], _dims(fixed), n, Ah, Ad, _MODE[mode],
+                                         float(frange[0]), float(frange[1]), float(mrange[0]), float(mrange[1]),
+                                         int(bins), ws.hist.data_ptr(), ws.count.data_ptr(), ws.ws.data_ptr(),
+                                         ws.ws.numel(), _stream(mov)))
+    return ws.hist[:n], ws.count[:n]
+
+
+def mi_from_hist(hist, out=None):
+    """MI (nats, float64) of each ``[bins, bins]`` integer histogram in ``hist`` ([n, bins, bins] int32)."""
+    lib = _lib.load()
+    if hist.dim() == 2:
+        hist = hist[None]
+    hist = hist.contiguous()
+    n, bins = hist.shape[0], hist.shape[1]
+    if out is None:
+        out = torch.empty(n, dtype=torch.float64, device=hist.device)
+    with torch.cuda.device(hist.device):
+        check(lib.mia_mi_from_hist(hist.data_ptr(), bins, n, out.data_ptr(), _stream(hist)))
+    return out
+
+
+def autocrop_extent(M, p2w_mov, mdims, out_spacing, extent_rule="round"):
+    """Host helper mirroring ``geometry.autocrop_extent`` through the C ABI."""
+    lib = _lib.load()
+    od = (ctypes.c_int * 3)()
+    oo = (ctypes.c_double * 3)()
+    check(lib.mia_autocrop_extent(darr(np.asarray(M, dtype=np.float64).ravel()),
+                                  darr(np.asarray(p2w_mov, dtype=np.float64).ravel()), i3(mdims),
+                                  darr(out_spacing), 0 if extent_rule == "round" else 1, od, oo))
+    return tuple(oo), tuple(od)

@@ -1,0 +1,191 @@
+"""Intensity-based rigid registration loop over the fused resample + metric kernels.
+
+The reference has no such loop (rigid = mesh ICP ``utils/rigid/icp.py:62-149`` or manual nudges
+``structure/rigid.py:950-989``); what is preserved from it is the parameterisation -- 'xyz' Euler degrees
+about the fixed-image centre composed as ``T(c) R T(-c)``, translations in mm -- and the ITK usage pattern
+of ``utils/deformable/simpleitk.py:114-124`` (metric + optimiser + linear interpolator, N iterations).
+
+Algorithm (identical on host and device, so CPU-oracle and GPU runs can be compared step for step):
+regular-step gradient descent on the 6 parameters with central finite differences -- 13 probes per
+iteration (centre, +-h_i per parameter) -- a unit step in scaled-parameter space, and step halving with a
+restore of the previous centre whenever the centre cost rises.  ``host_optimizer`` is the plain-Python
+statement of it with a pluggable ``evaluate``; ``register_rigid`` runs it on the GPU with the 13 probes
+batched into ONE fused launch per iteration and the update done by a one-thread kernel
+(``csrc/mia_optimizer.cuh``), so no scalar crosses PCIe inside the loop and the loop replays as a CUDA graph.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import geometry as G
+
+N_PROBES = 13
+
+
+@dataclass
+class RegistrationConfig:
+    metric: str = "ssd"              # 'ssd' (mean squares, minimised) or 'mi' (joint-histogram MI, maximised)
+    iterations: int = 200
+    rot_step_deg: float = 0.5        # probe offset and step length per unit scale, rotations
+    trans_step_mm: float = 0.5       # same, translations
+    min_step_scale: float = 1.0 / 1024.0
+    bins: int = 64
+    mode: str = "itk"                # inside test of the metric (ITK half-open)
+    frange: tuple | None = None      # intensity ranges for MI; None -> from the volumes, once
+    mrange: tuple | None = None
+    graph_iters: int = 10            # iterations captured per CUDA graph (0 = no graph)
+
+
+@dataclass
+class RegistrationResult:
+    params: np.ndarray
+    matrix: np.ndarray               # 4x4 fixed physical -> moving physical
+    iterations: int
+    converged: bool
+    n_reject: int
+    cost_history: np.ndarray
+    param_history: np.ndarray
+    scale_history: np.ndarray
+    evaluations: int = 0
+    extra: dict = field(default_factory=dict)
+
+
+def probe_params(params, scale, deltas):
+    """The 13 parameter vectors of one iteration: centre, then +h_i, -h_i for i = 0..5."""
+    p = np.asarray(params, dtype=np.float64)
+    out = [p.copy()]
+    for i in range(6):
+        h = scale * deltas[i]
+        a = p.copy(); a[i] += h
+        b = p.copy(); b[i] -= h
+        out += [a, b]
+    return out
+
+
+def params_to_index_matrix(params, center, p2w_fixed, w2p_mov):
+    """params -> 3x4 A (fixed index -> moving continuous index)."""
+    M = G.params_to_matrix(params, center)
+    return (w2p_mov @ M @ p2w_fixed)[:3, :]
+
+
+def host_optimizer(evaluate, params0, cfg: RegistrationConfig):
+    """Reference statement of the optimiser.  ``evaluate(list_of_13_param_vectors) -> 13 costs`` (lower is
+    better).  Mirrors ``optimizer_step_kernel`` line for line."""
+    deltas = np.array([cfg.rot_step_deg] * 3 + [cfg.trans_step_mm] * 3, dtype=np.float64)
+    params = np.asarray(params0, dtype=np.float64).copy()
+    prev_params = params.copy()
+    prev_cost, has_prev = 0.0, False
+    scale, converged, n_reject = 1.0, False, 0
+    hc, hp, hs = [], [], []
+    for _ in range(cfg.iterations):
+        c = np.asarray(evaluate(probe_params(params, scale, deltas)), dtype=np.float64)
+        hc.append(c[0]); hp.append(params.copy()); hs.append(scale)
+        if converged:
+            continue
+        if has_prev and c[0] > prev_cost:
+            params = prev_params.copy()
+            scale *= 0.5
+            n_reject += 1
+            if scale < cfg.min_step_scale:
+                converged = True
+        else:
+            prev_params = params.copy()
+            prev_cost, has_prev = c[0], True
+            sg = np.empty(6)
+            for i in range(6):
+                h = scale * deltas[i]
+                sg[i] = (c[2 * i + 1] - c[2 * i + 2]) / (2.0 * h) * deltas[i]
+            norm = float(np.sqrt(np.sum(sg * sg)))
+            if 0.0 < norm < 1.0e300:
+                params = params - scale * deltas * (sg / norm)
+            else:
+                converged = True
+    return RegistrationResult(params=params, matrix=None, iterations=len(hc), converged=converged,
+                              n_reject=n_reject, cost_history=np.array(hc), param_history=np.array(hp),
+                              scale_history=np.array(hs), evaluations=N_PROBES * len(hc))
+
+
+def _intensity_range(t):
+    return float(t.min().item()), float(t.max().item())
+
+
+def register_rigid(fixed, moving, params0=None, cfg: RegistrationConfig | None = None):
+    """Register ``moving`` to ``fixed`` (both ``structure.Image``-like with CUDA arrays) entirely on the GPU.
+
+    Returns a ``RegistrationResult``; ``result.matrix`` maps fixed physical -> moving physical, i.e. it is
+    what ``Rigid.matrix`` holds (``structure/rigid.py:674-686``)."""
+    import torch
+
+    from . import _lib, kernels
+    lib = _lib.load()
+    cfg = cfg or RegistrationConfig()
+    params0 = np.zeros(6) if params0 is None else np.asarray(params0, dtype=np.float64)
+    dev = fixed.array.device
+    center = np.asarray(fixed.compute_center(), dtype=np.float64)
+    p2w = G.index_to_physical(fixed.grid, "itk")
+    w2p = G.physical_to_index(moving.grid, "itk")
+    is_ssd = cfg.metric == "ssd"
+    if cfg.metric not in ("ssd", "mi"):
+        raise ValueError("metric must be 'ssd' or 'mi'")
+    ws = kernels.MetricWorkspace(dev, n_mats=N_PROBES, bins=cfg.bins)
+    d_A = torch.zeros((N_PROBES, 3, 4), dtype=torch.float64, device=dev)
+    state = torch.zeros(int(lib.mia_optimizer_state_bytes()), dtype=torch.uint8, device=dev)
+    if not is_ssd:
+        frange = cfg.frange or _intensity_range(fixed.array)
+        mrange = cfg.mrange or _intensity_range(moving.array)
+
+    def stream():
+        return ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+    with torch.cuda.device(dev):
+        _lib.check(lib.mia_optimizer_init(state.data_ptr(), _lib.darr(params0), _lib.darr(center),
+                                          _lib.darr(p2w.ravel()), _lib.darr(w2p.ravel()), cfg.rot_step_deg,
+                                          cfg.trans_step_mm, cfg.min_step_scale, 0 if is_ssd else 1,
+                                          d_A.data_ptr(), stream()))
+
+        def one_iteration():
+            if is_ssd:
+                kernels.resample_ssd(fixed.array, moving.array, d_A=d_A, mode=cfg.mode, ws=ws)
+                metric = ws.ssd
+            else:
+                kernels.resample_jointhist(fixed.array, moving.array, frange, mrange, bins=cfg.bins, d_A=d_A,
+                                           mode=cfg.mode, ws=ws)
+                kernels.mi_from_hist(ws.hist, out=ws.mi)
+                metric = ws.mi
+            _lib.check(lib.mia_optimizer_step(state.data_ptr(), metric.data_ptr(), ws.count.data_ptr(),
+                                              1 if is_ssd else 0, d_A.data_ptr(), stream()))
+
+        done = 0
+        gi = int(cfg.graph_iters)
+        if gi > 0 and cfg.iterations >= gi:
+            one_iteration()                       # warm-up outside capture (lazy module load, attributes)
+            done = 1
+            torch.cuda.synchronize(dev)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                for _ in range(gi):
+                    one_iteration()
+            while cfg.iterations - done >= gi:
+                graph.replay()
+                done += gi
+        while done < cfg.iterations:
+            one_iteration()
+            done += 1
+
+        n = min(cfg.iterations, 4096)
+        params = (ctypes.c_double * 6)()
+        scale = ctypes.c_double()
+        iters, conv, nrej = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        hc = np.zeros(n); hp = np.zeros((n, 6)); hs = np.zeros(n)
+        dp = ctypes.POINTER(ctypes.c_double)
+        _lib.check(lib.mia_optimizer_read(state.data_ptr(), params, ctypes.byref(scale), ctypes.byref(iters),
+                                          ctypes.byref(conv), ctypes.byref(nrej), hc.ctypes.data_as(dp),
+                                          hp.ctypes.data_as(dp), hs.ctypes.data_as(dp), n, stream()))
+    p = np.array(list(params))
+    return RegistrationResult(params=p, matrix=G.params_to_matrix(p, center), iterations=int(iters.value),
+                              converged=bool(conv.value), n_reject=int(nrej.value), cost_history=hc[:iters.value],
+                              param_history=hp[:iters.value], scale_history=hs[:iters.value],
+                              evaluations=N_PROBES * int(iters.value))

@@ -1,0 +1,64 @@
+"""Oracle similarity metrics (test infrastructure only; see ``oracle/__init__.py``).
+
+The reference's own code contains NO similarity metric: SSD and mutual information
+appear only as option strings handed to SimpleITK / Elastix for deformable registration
+(``utils/deformable/simpleitk.py:115`` ``SetMetricAsMeanSquares``, ``:153`` "AdvancedMeanSquares",
+``:155-156`` "AdvancedMattesMutualInformation" + ``NumberOfHistogramBins``).  The definitions below
+are therefore this repository's written spec, shared word for word by the
+CUDA kernels:
+
+  M1  ssd = sum over fixed voxels whose sample is inside (ITK half-open test) of (F - m)^2, m the
+      UNROUNDED interpolated moving value; n_valid = number of such voxels; mse = ssd / n_valid.
+  M2  joint histogram H[bf][bm], B bins per axis, bf = clamp(floor((F - fmin) * B / (fmax - fmin)), 0, B-1),
+      bm likewise from m; hard binning over the same valid voxels; MI = sum p_ij ln(p_ij / (p_i. p_.j))
+      in float64 from the integer counts (natural log).
+PARITY UNPINNED by the reference: there is nothing in it to pin these against.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from .reslice import oracle_reslice
+
+
+def bin_index(v, vmin, vmax, bins):
+    """The binning arithmetic is done in float32 exactly as the kernel does it
+    (scale = B / (max - min) rounded to f32; (v - min) * scale in f32; floor; clamp)."""
+    v = np.asarray(v, dtype=np.float32)
+    scale = np.float32(bins) / (np.float32(vmax) - np.float32(vmin))
+    b = np.floor((v - np.float32(vmin)) * scale)
+    return np.clip(b, 0, bins - 1).astype(np.int64)
+
+
+def oracle_ssd(fixed, mov, A, mode="itk"):
+    """(ssd float64, n_valid int).  ``fixed`` defines the output lattice ([z,y,x])."""
+    fixed = np.asarray(fixed)
+    odims = (fixed.shape[2], fixed.shape[1], fixed.shape[0])
+    _, vals, mask = oracle_reslice(mov, A, odims, 0.0, mode, np.float32, return_float=True)
+    d = fixed.astype(np.float64) - vals
+    d = d[mask]
+    return float(np.sum(d * d)), int(mask.sum())
+
+
+def oracle_joint_hist(fixed, mov, A, bins, frange, mrange, mode="itk"):
+    """(H uint64 [bins, bins] indexed [fixed_bin, moving_bin], n_valid)."""
+    fixed = np.asarray(fixed)
+    odims = (fixed.shape[2], fixed.shape[1], fixed.shape[0])
+    _, vals, mask = oracle_reslice(mov, A, odims, 0.0, mode, np.float32, return_float=True)
+    bf = bin_index(fixed[mask], frange[0], frange[1], bins)
+    bm = bin_index(vals[mask].astype(np.float32), mrange[0], mrange[1], bins)
+    H = np.bincount(bf * bins + bm, minlength=bins * bins).reshape(bins, bins).astype(np.uint64)
+    return H, int(mask.sum())
+
+
+def oracle_mi(H):
+    """Mutual information (nats) of an integer joint histogram, float64."""
+    H = np.asarray(H, dtype=np.float64)
+    n = H.sum()
+    if n <= 0:
+        return 0.0
+    pf = H.sum(axis=1)
+    pm = H.sum(axis=0)
+    nzf, nzm = np.nonzero(H)
+    h = H[nzf, nzm]
+    return float(np.sum((h / n) * np.log(h * n / (pf[nzf] * pm[nzm]))))
