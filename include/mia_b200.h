@@ -47,6 +47,9 @@ extern "C" {
 
 int mia_version(void);
 const char *mia_last_error(void);
+/* Diagnostic: which kernel the calling thread's last resample / metric call launched
+ * (0 = direct per-voxel kernel, 1 = TMA-staged tile kernel).  Used by the parity tests. */
+int mia_debug_last_path(void);
 
 /*
  * Rigid trilinear resample of a device-resident moving volume onto an output lattice.

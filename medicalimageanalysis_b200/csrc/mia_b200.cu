@@ -9,8 +9,12 @@
 #include <string>
 #include <vector>
 
+#include <cstdlib>
+#include <map>
+
 #include "mia_kernels.cuh"
 #include "mia_optimizer.cuh"
+#include "mia_tile.cuh"
 
 using namespace mia;
 
@@ -120,6 +124,147 @@ void dispatch_metric(int mov_dtype, int fixed_dtype, const KParams &p, int mode,
         launch_metric<float, float, METRIC, STORE>(p, mode, grid, smem, s);
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// Tile kernel dispatch (mia_tile.cuh).  The tile path needs a TMA descriptor of the moving volume:
+// 16-byte aligned base and row pitch.  Anything else goes to the direct kernel.
+thread_local int g_last_path = 0;    // 0 = direct kernel, 1 = tile kernel (diagnostic, mia_debug_last_path)
+
+template <typename TM> struct BoxFor;
+template <> struct BoxFor<int16_t> { using type = Box<48, 18, 16>; };
+template <> struct BoxFor<float>   { using type = Box<40, 18, 14>; };
+constexpr int kTileStages = 2;
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled_fn()
+{
+    static EncodeTiledFn fn = [] {
+        void *f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            f = nullptr;
+        return reinterpret_cast<EncodeTiledFn>(f);
+    }();
+    return fn;
+}
+
+bool tile_path_disabled()
+{
+    static const bool off = [] {
+        const char *e = getenv("MIA_FORCE_DIRECT");
+        return e && e[0] && e[0] != '0';
+    }();
+    return off;
+}
+
+// Builds the 3-D tensor map of the moving volume with the box of BoxFor<TM>.  False => not eligible.
+template <typename TM>
+bool make_tensor_map(CUtensorMap *map, const void *d_mov, const int mdims[3])
+{
+    using BOX = typename BoxFor<TM>::type;
+    if (tile_path_disabled()) return false;
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) return false;
+    const size_t es = sizeof(TM);
+    if (((uintptr_t)d_mov & 15u) != 0 || ((size_t)mdims[0] * es) % 16 != 0) return false;
+    const cuuint64_t gdim[3] = {(cuuint64_t)mdims[0], (cuuint64_t)mdims[1], (cuuint64_t)mdims[2]};
+    const cuuint64_t gstr[2] = {(cuuint64_t)mdims[0] * es, (cuuint64_t)mdims[0] * mdims[1] * es};
+    const cuuint32_t box[3] = {BOX::kX, BOX::kY, BOX::kZ};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUtensorMapDataType dt = es == 2 ? CU_TENSOR_MAP_DATA_TYPE_UINT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+    const CUresult r = enc(map, dt, 3, const_cast<void *>(d_mov), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS;
+}
+
+// Does a typical tile of this host matrix fit the box?  (Device matrices are classified per tile.)
+template <typename TM>
+bool box_fits(const double *A)
+{
+    using BOX = typename BoxFor<TM>::type;
+    const Reach r = tile_reach(A);
+    const int B[3] = {BOX::kX, BOX::kY, BOX::kZ};
+    for (int a = 0; a < 3; ++a)
+        if (std::ceil(r.pos[a] - r.neg[a]) + 3.0 + (a == 0 ? 16.0 / sizeof(TM) - 1.0 : 0.0) > (double)B[a]) return false;
+    return true;
+}
+
+void fill_tile(KParams &p)
+{
+    p.ntx = (p.ox + kTX - 1) / kTX;
+    p.nty = (p.oy + kTY - 1) / kTY;
+    p.ntiles = (long long)p.ntx * p.nty * ((p.oz + kTZ - 1) / kTZ);
+}
+
+template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK>
+int launch_tile(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream_t s)
+{
+    using BOX = typename BoxFor<TM>::type;
+    constexpr int MINB = sizeof(TM) == 2 ? 3 : 2;
+    auto k = tile_kernel<TM, TF, TO, METRIC, STORE, VTK, BOX, kTileStages, MINB>;
+    const size_t smem = TileSmem<TM, BOX, kTileStages>::bytes(METRIC == kHist ? p.bins : 0);
+    static std::mutex mu;
+    static std::map<std::pair<int, size_t>, int> occ;     // (device, smem) -> resident CTAs per SM
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    int nb = 0;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        auto it = occ.find({dev, smem});
+        if (it == occ.end()) {
+            CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k, kTileThreads, smem));
+            if (nb < 1) return fail(MIA_ERR_UNSUPPORTED, "tile kernel does not fit on this device (%zu B smem)", smem);
+            occ[{dev, smem}] = nb;
+        } else {
+            nb = it->second;
+        }
+    }
+    long long gx = (long long)sm_count() * nb;
+    if (gx > p.ntiles) gx = p.ntiles;
+    if (gx > kMaxGridX) gx = kMaxGridX;
+    dim3 grid((unsigned)gx, (unsigned)n_mats, 1);
+    k<<<grid, kTileThreads, smem, s>>>(map, p);
+    CUDA_TRY(cudaGetLastError());
+    g_last_path = 1;
+    return MIA_OK;
+}
+
+
+// Try the tile path for (dtype, mode); `launched` tells whether it took the call.  A_host may be null
+// (device matrices: the kernel classifies every tile itself and falls back per tile).
+template <int METRIC, bool STORE>
+int try_tile(int dtype, int mode, const void *d_mov, const int mdims[3], const double *A_host, int n_mats,
+             KParams p, cudaStream_t s, bool &launched)
+{
+    launched = false;
+    alignas(64) CUtensorMap map;
+    const bool vtk = mode == MIA_MODE_VTK;
+    if (dtype == MIA_I16) {
+        for (int m = 0; A_host && m < n_mats; ++m)
+            if (!box_fits<int16_t>(A_host + 12 * m)) return MIA_OK;
+        if (!make_tensor_map<int16_t>(&map, d_mov, mdims)) return MIA_OK;
+    } else {
+        for (int m = 0; A_host && m < n_mats; ++m)
+            if (!box_fits<float>(A_host + 12 * m)) return MIA_OK;
+        if (!make_tensor_map<float>(&map, d_mov, mdims)) return MIA_OK;
+    }
+    fill_tile(p);
+    if (p.ntiles > 0x7fffffffLL) return MIA_OK;
+    if ((long long)p.ox * p.oy * kTZ >= 0x7fffffffLL) return MIA_OK;   // in-tile plane offsets are 32-bit
+    launched = true;
+    if (dtype == MIA_I16)
+        return vtk ? launch_tile<int16_t, int16_t, int16_t, METRIC, STORE, true>(map, p, n_mats, s)
+                   : launch_tile<int16_t, int16_t, int16_t, METRIC, STORE, false>(map, p, n_mats, s);
+    return vtk ? launch_tile<float, float, float, METRIC, STORE, true>(map, p, n_mats, s)
+               : launch_tile<float, float, float, METRIC, STORE, false>(map, p, n_mats, s);
+}
+
 }  // namespace
 
 extern "C" {
@@ -127,6 +272,8 @@ extern "C" {
 int mia_version(void) { return MIA_B200_VERSION; }
 
 const char *mia_last_error(void) { return g_err.c_str(); }
+
+int mia_debug_last_path(void) { return g_last_path; }
 
 int mia_resample_rigid(const void *d_mov, int mov_dtype, const int mdims[3], void *d_out, int out_dtype,
                        const int odims[3], const double A[12], double background, int mode, void *stream)
@@ -147,6 +294,12 @@ int mia_resample_rigid(const void *d_mov, int mov_dtype, const int mdims[3], voi
     if (p.ntiles > 0x7fffffffLL) return fail(MIA_ERR_UNSUPPORTED, "mia_resample_rigid: output too large");
     dim3 grid((unsigned)p.ntiles, 1, 1);
     cudaStream_t s = (cudaStream_t)stream;
+    g_last_path = 0;
+    if (mov_dtype == out_dtype) {
+        bool launched = false;
+        const int rc = try_tile<kNone, true>(mov_dtype, mode, d_mov, mdims, A, 1, p, s, launched);
+        if (launched) return rc;
+    }
     if (mov_dtype == MIA_I16 && out_dtype == MIA_I16) launch_resample<int16_t, int16_t>(p, mode, grid, s);
     else if (mov_dtype == MIA_I16 && out_dtype == MIA_F32) launch_resample<int16_t, float>(p, mode, grid, s);
     else if (mov_dtype == MIA_F32 && out_dtype == MIA_I16) launch_resample<float, int16_t>(p, mode, grid, s);
@@ -225,6 +378,13 @@ int mia_resample_ssd(const void *d_mov, int mov_dtype, const int mdims[3], const
     if (gx > p.ntiles) gx = p.ntiles;
     if (gx > kMaxGridX) gx = kMaxGridX;
     dim3 grid((unsigned)gx, (unsigned)n_mats, 1);
+    g_last_path = 0;
+    if (mov_dtype == fixed_dtype) {
+        bool launched = false;
+        const int trc = d_out ? try_tile<kSsd, true>(mov_dtype, mode, d_mov, mdims, d_A ? nullptr : A, n_mats, p, s, launched)
+                              : try_tile<kSsd, false>(mov_dtype, mode, d_mov, mdims, d_A ? nullptr : A, n_mats, p, s, launched);
+        if (launched) return trc;
+    }
     if (d_out) dispatch_metric<kSsd, true>(mov_dtype, fixed_dtype, p, mode, grid, 0, s);
     else dispatch_metric<kSsd, false>(mov_dtype, fixed_dtype, p, mode, grid, 0, s);
     CUDA_TRY(cudaGetLastError());
@@ -257,6 +417,12 @@ int mia_resample_jointhist(const void *d_mov, int mov_dtype, const int mdims[3],
     if (gx > p.ntiles) gx = p.ntiles;
     if (gx > kMaxGridX) gx = kMaxGridX;
     dim3 grid((unsigned)gx, (unsigned)n_mats, 1);
+    g_last_path = 0;
+    if (mov_dtype == fixed_dtype) {
+        bool launched = false;
+        const int trc = try_tile<kHist, false>(mov_dtype, mode, d_mov, mdims, d_A ? nullptr : A, n_mats, p, s, launched);
+        if (launched) return trc;
+    }
     dispatch_metric<kHist, false>(mov_dtype, fixed_dtype, p, mode, grid, smem, s);
     CUDA_TRY(cudaGetLastError());
     return MIA_OK;

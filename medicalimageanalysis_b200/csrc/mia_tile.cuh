@@ -1,0 +1,514 @@
+// TMA-staged tile kernel of the rigid resample + metric hot path (sm_100a).
+//
+// Why: the direct kernel in mia_kernels.cuh spends ~200 lane-instructions per output voxel (64-bit
+// index math, six clamps, eight LDG, float64 setup per 4 voxels) and is issue-bound at 7 % of the HBM
+// roofline.  Here the moving-volume box an output tile touches is staged in shared memory by TMA
+// (cp.async.bulk.tensor.3d, zero instructions in the compute warps, zero fill outside the volume) and
+// the gather becomes 8 LDS with compile-time offsets + 8 I2FP + 7 lerps on thread-local float32
+// coordinates: ~50 lane-instructions per voxel.
+//
+// Shape: persistent CTAs of 9 warps.  Warp 8 (one lane) is the TMA producer: per tile it maps the tile
+// origin through A in float64, classifies the tile (outside / interior / border / does-not-fit) and
+// issues one 3-D box copy into a kStages-deep ring guarded by full/empty mbarriers.  Warps 0..7 are
+// consumers: an output tile is 32 (x) x 8 (y) x 8 (z); lane = x (so LDS and the fixed/out accesses of a
+// warp are contiguous), warp = y row, each thread walks the 8 z planes of the tile.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "mia_kernels.cuh"
+
+namespace mia {
+
+constexpr int kTX = 32, kTY = 8, kTZ = 8;       // output tile
+constexpr int kConsumerWarps = kTY;
+constexpr int kTileThreads = 32 * (kConsumerWarps + 1);
+
+enum TileClass { kOutside = 0, kInterior = 1, kBorder = 2, kNoFit = 3 };
+
+template <int X, int Y, int Z>
+struct Box {
+    static constexpr int kX = X, kY = Y, kZ = Z;
+};
+
+struct TileInfo {          // producer -> consumers, one per ring stage
+    double c0x, c0y, c0z;  // continuous moving index of the tile's first voxel
+    int bx, by, bz;        // moving index of box element [0][0][0]
+    int cls;
+};
+
+// ---- mbarrier / TMA primitives (inline PTX; no CUTLASS dependency) ------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+
+__device__ __forceinline__ void mbar_arrive(uint32_t bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(bar), "r"(parity)
+        : "memory");
+}
+
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int x, int y, int z)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+        ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(z), "r"(bar)
+        : "memory");
+}
+
+// floor through the mantissa: (l + 1.5*2^23) rounded toward -inf keeps floor(l) in the low mantissa bits
+constexpr float kMagic = 12582912.0f;
+constexpr uint32_t kMagicBits = 0x4B400000u;
+
+__device__ __forceinline__ float add_rm(float a, float b)
+{
+    float r;
+    asm("add.rm.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
+}
+
+template <typename TO, bool VTK>
+__device__ __forceinline__ TO tile_to_out(float v);
+
+template <>
+__device__ __forceinline__ float tile_to_out<float, true>(float v) { return v; }
+template <>
+__device__ __forceinline__ float tile_to_out<float, false>(float v) { return v; }
+template <>
+__device__ __forceinline__ int16_t tile_to_out<int16_t, true>(float v)   // floor(v + 0.5), saturated
+{
+    short r;
+    asm("cvt.rmi.sat.s16.f32 %0, %1;" : "=h"(r) : "f"(v + 0.5f));
+    return r;
+}
+template <>
+__device__ __forceinline__ int16_t tile_to_out<int16_t, false>(float v)  // trunc(v), saturated
+{
+    short r;
+    asm("cvt.rzi.sat.s16.f32 %0, %1;" : "=h"(r) : "f"(v));
+    return r;
+}
+
+// Extent of one output tile in moving index space: negative / positive reach from the tile origin.
+struct Reach {
+    double neg[3], pos[3];
+};
+
+__host__ __device__ inline Reach tile_reach(const double *A)
+{
+    Reach r;
+    const double ext[3] = {(double)(kTX - 1), (double)(kTY - 1), (double)(kTZ - 1)};
+    for (int a = 0; a < 3; ++a) {
+        double n = 0.0, q = 0.0;
+        for (int c = 0; c < 3; ++c) {
+            const double d = A[a * 4 + c] * ext[c];
+            if (d < 0.0) n += d; else q += d;
+        }
+        r.neg[a] = n;
+        r.pos[a] = q;
+    }
+    return r;
+}
+
+// Classify one tile and choose its box.  Shared by the device producer and the host (launch heuristics,
+// unit tests).  `closed` only matters for ties and is folded into the conservative tests below.
+// TMA constraint measured on B200 (tests/cuda/tma_probe3.cu): with INTERLEAVE_NONE the innermost box
+// coordinate times the element size must be a multiple of 16 bytes, otherwise the copy raises "illegal
+// instruction".  The box origin along x is therefore rounded down to `xalign` (= 16 / sizeof(element)) voxels.
+template <class BOX>
+__host__ __device__ inline TileInfo classify_tile(const double *A, const Reach &r, int i0, int j0, int k0,
+                                                  int nx, int ny, int nz, int xalign)
+{
+    TileInfo t;
+    const double c0[3] = {((A[3] + (double)k0 * A[2]) + (double)j0 * A[1]) + (double)i0 * A[0],
+                          ((A[7] + (double)k0 * A[6]) + (double)j0 * A[5]) + (double)i0 * A[4],
+                          ((A[11] + (double)k0 * A[10]) + (double)j0 * A[9]) + (double)i0 * A[8]};
+    t.c0x = c0[0]; t.c0y = c0[1]; t.c0z = c0[2];
+    const int n[3] = {nx, ny, nz};
+    const int B[3] = {BOX::kX, BOX::kY, BOX::kZ};
+    int b[3] = {0, 0, 0};
+    bool outside = false, interior = true, fits = true;
+    for (int a = 0; a < 3; ++a) {
+        const double lo = c0[a] + r.neg[a], hi = c0[a] + r.pos[a];
+        if (!(hi >= -0.5) || !(lo <= (double)n[a] - 0.5)) { outside = true; continue; }   // NaN -> outside
+        if (!(lo >= 0.0 && hi <= (double)(n[a] - 1))) interior = false;
+        const double top = (double)(n[a] - 1);
+        double lc = lo < 0.0 ? 0.0 : (lo > top ? top : lo);
+        double hc = hi < 0.0 ? 0.0 : (hi > top ? top : hi);
+        lc -= 1.0e-3;                      // float32 thread coordinates may stray ~1e-6 beyond the AABB
+        hc += 1.0e-3;
+        const double fh = floor(hc);
+        b[a] = (int)floor(lc);
+        if (a == 0) b[a] &= ~(xalign - 1);          // two's complement: rounds toward -inf for negatives too
+        if (fh + 2.0 - (double)b[a] > (double)B[a]) fits = false;
+    }
+    t.bx = b[0]; t.by = b[1]; t.bz = b[2];
+    t.cls = outside ? kOutside : (!fits ? kNoFit : (interior ? kInterior : kBorder));
+    return t;
+}
+
+
+__device__ __forceinline__ float prev_float(float h)
+{
+    const int b = __float_as_int(h);
+    return __int_as_float(h > 0.0f ? b - 1 : (h < 0.0f ? b + 1 : (int)0x80000001));
+}
+
+// Shared-memory tap -> float32.  int16 is loaded sign-extended (LDS.S16) so that the conversion is the
+// half-rate ALU I2FP.F32.S32 and not the quarter-rate XU I2F.S16 the compiler picks for a C++ short load.
+template <int BYTE_OFF>
+__device__ __forceinline__ float tap_i16(uint32_t addr)
+{
+    int v;
+    asm volatile("ld.shared.s16 %0, [%1+%2];" : "=r"(v) : "r"(addr), "n"(BYTE_OFF));
+    return (float)v;
+}
+template <int BYTE_OFF>
+__device__ __forceinline__ float tap_f32(uint32_t addr)
+{
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(v) : "r"(addr), "n"(BYTE_OFF));
+    return v;
+}
+template <typename TM, int BYTE_OFF>
+struct Tap;
+template <int BYTE_OFF>
+struct Tap<int16_t, BYTE_OFF> {
+    static __device__ __forceinline__ float ld(uint32_t a) { return tap_i16<BYTE_OFF>(a); }
+};
+template <int BYTE_OFF>
+struct Tap<float, BYTE_OFF> {
+    static __device__ __forceinline__ float ld(uint32_t a) { return tap_f32<BYTE_OFF>(a); }
+};
+
+__device__ __forceinline__ void st_out(int16_t *p, int16_t v) { asm volatile("st.global.cs.u16 [%0], %1;" ::"l"(p), "h"(v) : "memory"); }
+__device__ __forceinline__ void st_out(float *p, float v) { asm volatile("st.global.cs.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory"); }
+
+// One consumer thread's share of one tile whose box is resident in shared memory: the 8 z planes of
+// output voxel column (i0 + lane, j0 + warp).  BORDER adds the inside test and the coordinate clamp
+// (== VTK/ITK index clamp: the clamped coordinate has weight 0 on the tap beyond the edge, which TMA
+// zero-filled); interior tiles need neither.
+template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, bool BORDER, class BOX>
+__device__ __forceinline__ void tile_compute(const KParams &p, const unsigned char *stage, const TileInfo &ti,
+                                             const double *A, int i0, int j0, int k0, int lane, int warp,
+                                             double &acc, unsigned &cnt, unsigned *s_hist)
+{
+    constexpr unsigned ES = sizeof(TM);
+    constexpr int PY = BOX::kX * ES, PZ = BOX::kX * BOX::kY * ES;
+    const int i = i0 + lane, j = j0 + warp;
+    const bool row_ok = (i < p.ox) & (j < p.oy);
+    const int kcnt = min(kTZ, p.oz - k0);
+
+    // thread base in float64, split into an integer box offset and a float32 fraction
+    const double rx = fma((double)lane, A[0], fma((double)warp, A[1], ti.c0x)) - (double)ti.bx;
+    const double ry = fma((double)lane, A[4], fma((double)warp, A[5], ti.c0y)) - (double)ti.by;
+    const double rz = fma((double)lane, A[8], fma((double)warp, A[9], ti.c0z)) - (double)ti.bz;
+    const int tbx = __double2int_rd(rx), tby = __double2int_rd(ry), tbz = __double2int_rd(rz);
+    const float fx = (float)(rx - (double)tbx), fy = (float)(ry - (double)tby), fz = (float)(rz - (double)tbz);
+    const float a2x = (float)A[2], a2y = (float)A[6], a2z = (float)A[10];
+    // element index = ((iz*BY + iy)*BX + ix) with i* = thread base + floor(local); floor(local) arrives as the
+    // raw bits of (local + kMagic), i.e. kMagicBits + floor: the constant part is folded into ubase (mod 2^32)
+    const uint32_t ubase = smem_u32(stage) +
+                           ((uint32_t)((tbz * BOX::kY + tby) * BOX::kX + tbx) -
+                            kMagicBits * (uint32_t)((BOX::kY + 1) * BOX::kX + 1)) * ES;
+
+    float ilox = 0.f, ihix = 0.f, iloy = 0.f, ihiy = 0.f, iloz = 0.f, ihiz = 0.f;
+    float clox = 0.f, chix = 0.f, cloy = 0.f, chiy = 0.f, cloz = 0.f, chiz = 0.f;
+    if (BORDER) {
+        const float gx = (float)(ti.bx + tbx), gy = (float)(ti.by + tby), gz = (float)(ti.bz + tbz);
+        ilox = -0.5f - gx; iloy = -0.5f - gy; iloz = -0.5f - gz;
+        ihix = (float)p.mov.nx - 0.5f - gx; ihiy = (float)p.mov.ny - 0.5f - gy; ihiz = (float)p.mov.nz - 0.5f - gz;
+        if (!VTK) { ihix = prev_float(ihix); ihiy = prev_float(ihiy); ihiz = prev_float(ihiz); }
+        clox = -gx; cloy = -gy; cloz = -gz;
+        chix = (float)(p.mov.nx - 1) - gx; chiy = (float)(p.mov.ny - 1) - gy; chiz = (float)(p.mov.nz - 1) - gz;
+    }
+
+    // the host guarantees 8 * oy * ox < 2^31, so plane offsets inside a tile are 32-bit
+    const unsigned plane = (unsigned)p.oy * (unsigned)p.ox;
+    const size_t gofs = ((size_t)k0 * p.oy + j) * p.ox + i;
+    const TF *fixed = static_cast<const TF *>(p.fixed) + gofs;
+    TO *out = static_cast<TO *>(p.out) + gofs;
+    const TO bgv = tile_to_out<TO, VTK>(p.background);
+
+    float fv[kTZ];
+    if (METRIC != kNone) {
+#pragma unroll
+        for (int kz = 0; kz < kTZ; ++kz)
+            fv[kz] = (row_ok && kz < kcnt) ? (float)__ldg(fixed + (unsigned)kz * plane) : 0.0f;
+    }
+
+    float part = 0.0f;
+#pragma unroll
+    for (int kz = 0; kz < kTZ; ++kz) {
+        float lx = fmaf((float)kz, a2x, fx), ly = fmaf((float)kz, a2y, fy), lz = fmaf((float)kz, a2z, fz);
+        bool in = true;
+        if (BORDER) {
+            in = (lx >= ilox) & (lx <= ihix) & (ly >= iloy) & (ly <= ihiy) & (lz >= iloz) & (lz <= ihiz);
+            lx = fminf(fmaxf(lx, clox), chix);
+            ly = fminf(fmaxf(ly, cloy), chiy);
+            lz = fminf(fmaxf(lz, cloz), chiz);
+        }
+        const float tx = add_rm(lx, kMagic), ty = add_rm(ly, kMagic), tz = add_rm(lz, kMagic);
+        const float wx = lx - (tx - kMagic), wy = ly - (ty - kMagic), wz = lz - (tz - kMagic);
+        const uint32_t a = ((__float_as_uint(tz) * BOX::kY + __float_as_uint(ty)) * BOX::kX + __float_as_uint(tx)) * ES + ubase;
+        const float v000 = Tap<TM, 0>::ld(a), v100 = Tap<TM, ES>::ld(a);
+        const float v010 = Tap<TM, PY>::ld(a), v110 = Tap<TM, PY + ES>::ld(a);
+        const float v001 = Tap<TM, PZ>::ld(a), v101 = Tap<TM, PZ + ES>::ld(a);
+        const float v011 = Tap<TM, PZ + PY>::ld(a), v111 = Tap<TM, PZ + PY + ES>::ld(a);
+        const float vx00 = fmaf(wx, v100 - v000, v000);
+        const float vx10 = fmaf(wx, v110 - v010, v010);
+        const float vx01 = fmaf(wx, v101 - v001, v001);
+        const float vx11 = fmaf(wx, v111 - v011, v011);
+        const float vxx0 = fmaf(wy, vx10 - vx00, vx00);
+        const float vxx1 = fmaf(wy, vx11 - vx01, vx01);
+        const float val = fmaf(wz, vxx1 - vxx0, vxx0);
+        const bool live = row_ok && kz < kcnt;
+        if (STORE) {
+            const TO o = tile_to_out<TO, VTK>(val);
+            const TO r = in ? o : bgv;
+            if (live) st_out(out + (unsigned)kz * plane, r);
+        }
+        if (METRIC == kSsd) {
+            const float d = fv[kz] - val;
+            if (live && in) {
+                part = fmaf(d, d, part);
+                ++cnt;
+            }
+        }
+        if (METRIC == kHist) {
+            if (live && in) {
+                const int bf = bin_of(fv[kz], p.fmin, p.fscale, p.bins);
+                const int bm = bin_of(val, p.mmin, p.mscale, p.bins);
+                atomicAdd(&s_hist[bf * p.bins + bm], 1u);
+                ++cnt;
+            }
+        }
+    }
+    if (METRIC == kSsd) acc += (double)part;
+}
+
+// Tiles that need no box: entirely outside (background only) or too large for the box (per-voxel global
+// gather, the arithmetic of the direct kernel).  Rare; kept simple.
+template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK>
+__device__ __noinline__ void tile_compute_nobox(const KParams &p, const double *A, int cls, int i0, int j0, int k0,
+                                                int lane, int warp, double &acc, unsigned &cnt, unsigned *s_hist)
+{
+    const int i = i0 + lane, j = j0 + warp;
+    if (i >= p.ox || j >= p.oy) return;
+    const int kcnt = min(kTZ, p.oz - k0);
+    const TM *mov = static_cast<const TM *>(p.mov.p);
+    const size_t plane = (size_t)p.oy * p.ox;
+    const size_t gofs = ((size_t)k0 * p.oy + j) * p.ox + i;
+    const TF *fixed = static_cast<const TF *>(p.fixed) + gofs;
+    TO *out = static_cast<TO *>(p.out) + gofs;
+    const TO bgv = tile_to_out<TO, VTK>(p.background);
+    float part = 0.0f;
+    for (int kz = 0; kz < kcnt; ++kz) {
+        float val = 0.0f;
+        bool in = false;
+        if (cls != kOutside) {
+            const RowCtx r = make_row_ctx(A, i, j, k0 + kz, p.mov.nx, p.mov.ny, p.mov.nz);
+            in = sample_voxel<TM, VTK>(mov, p.mov.nx, p.mov.ny, p.mov.nz, r, 0, val);
+        }
+        if (STORE) out[(size_t)kz * plane] = in ? tile_to_out<TO, VTK>(val) : bgv;
+        if (METRIC != kNone && in) {
+            const float f = (float)__ldg(fixed + (size_t)kz * plane);
+            if (METRIC == kSsd) {
+                const float d = f - val;
+                part = fmaf(d, d, part);
+            } else {
+                atomicAdd(&s_hist[bin_of(f, p.fmin, p.fscale, p.bins) * p.bins + bin_of(val, p.mmin, p.mscale, p.bins)], 1u);
+            }
+            ++cnt;
+        }
+    }
+    if (METRIC == kSsd) acc += (double)part;
+}
+
+
+// Shared-memory carve-up of the tile kernel (dynamic): kStages boxes, 2*kStages mbarriers, kStages
+// TileInfo records, then the privatised joint histogram (METRIC == kHist).
+template <typename TM, class BOX, int NST>
+struct TileSmem {
+    static constexpr unsigned kBoxBytes = BOX::kX * BOX::kY * BOX::kZ * sizeof(TM);
+    static constexpr unsigned kStageBytes = (kBoxBytes + 127u) & ~127u;
+    static constexpr unsigned kBarOff = kStageBytes * NST;
+    static constexpr unsigned kInfoOff = kBarOff + 16u * NST;
+    static constexpr unsigned kHistOff = (kInfoOff + (unsigned)sizeof(TileInfo) * NST + 15u) & ~15u;
+    static size_t bytes(int bins) { return (size_t)kHistOff + sizeof(unsigned) * (size_t)bins * bins; }
+};
+
+template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, class BOX, int NST, int MINB>
+__global__ void __launch_bounds__(kTileThreads, MINB)
+tile_kernel(const __grid_constant__ CUtensorMap tmap, const KParams p)
+{
+    using L = TileSmem<TM, BOX, NST>;
+    extern __shared__ __align__(1024) unsigned char tsm[];
+    __shared__ double s_red[kTileThreads / 32];
+    __shared__ unsigned long long s_redc[kTileThreads / 32];
+    __shared__ bool s_last;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int m = blockIdx.y;
+    unsigned *s_hist = reinterpret_cast<unsigned *>(tsm + L::kHistOff);
+    TileInfo *infos = reinterpret_cast<TileInfo *>(tsm + L::kInfoOff);
+    const uint32_t bar0 = smem_u32(tsm + L::kBarOff);       // full[s] = bar0 + 8 s, empty[s] = bar0 + 8 (NST + s)
+
+    double A[12];
+    {
+        const double *Ap = p.dA ? p.dA + 12 * m : p.A0.a;
+#pragma unroll
+        for (int q = 0; q < 12; ++q) A[q] = Ap[q];
+    }
+
+    if (tid == 0) {
+        for (int s = 0; s < NST; ++s) {
+            mbar_init(bar0 + 8 * s, 1);
+            mbar_init(bar0 + 8 * (NST + s), kConsumerWarps);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (METRIC == kHist)
+        for (int b = tid; b < p.bins * p.bins; b += kTileThreads) s_hist[b] = 0u;
+    __syncthreads();
+
+    double acc = 0.0;
+    unsigned cnt = 0;
+
+    if (warp == kConsumerWarps) {
+        // ---------------- producer: one lane ----------------
+        if (lane == 0) {
+            const Reach reach = tile_reach(A);
+            unsigned n = 0;
+            for (long long tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++n) {
+                const unsigned s = n % NST, ph = (n / NST) & 1u;
+                mbar_wait(bar0 + 8 * (NST + s), ph ^ 1u);
+                const int tix = (int)(tile % p.ntx);
+                const long long t2 = tile / p.ntx;
+                const int tiy = (int)(t2 % p.nty), tiz = (int)(t2 / p.nty);
+                const TileInfo ti = classify_tile<BOX>(A, reach, tix * kTX, tiy * kTY, tiz * kTZ, p.mov.nx, p.mov.ny, p.mov.nz,
+                                                            16 / (int)sizeof(TM));
+                infos[s] = ti;
+                if (ti.cls == kInterior || ti.cls == kBorder) {
+                    mbar_arrive_expect_tx(bar0 + 8 * s, L::kBoxBytes);
+                    tma_load_3d(smem_u32(tsm + L::kStageBytes * s), &tmap, bar0 + 8 * s, ti.bx, ti.by, ti.bz);
+                } else {
+                    mbar_arrive(bar0 + 8 * s);
+                }
+            }
+        }
+    } else {
+        // ---------------- consumers: 8 warps ----------------
+        unsigned n = 0;
+        for (long long tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++n) {
+            const unsigned s = n % NST, ph = (n / NST) & 1u;
+            const int tix = (int)(tile % p.ntx);
+            const long long t2 = tile / p.ntx;
+            const int tiy = (int)(t2 % p.nty), tiz = (int)(t2 / p.nty);
+            const int i0 = tix * kTX, j0 = tiy * kTY, k0 = tiz * kTZ;
+            mbar_wait(bar0 + 8 * s, ph);
+            const TileInfo ti = infos[s];
+            const unsigned char *stage = tsm + L::kStageBytes * s;
+            if (ti.cls == kInterior)
+                tile_compute<TM, TF, TO, METRIC, STORE, VTK, false, BOX>(p, stage, ti, A, i0, j0, k0, lane, warp, acc, cnt, s_hist);
+            else if (ti.cls == kBorder)
+                tile_compute<TM, TF, TO, METRIC, STORE, VTK, true, BOX>(p, stage, ti, A, i0, j0, k0, lane, warp, acc, cnt, s_hist);
+            else if (STORE || ti.cls == kNoFit)
+                tile_compute_nobox<TM, TF, TO, METRIC, STORE, VTK>(p, p.dA ? p.dA + 12 * m : p.A0.a, ti.cls, i0, j0, k0, lane, warp,
+                                                                   acc, cnt, s_hist);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar0 + 8 * (NST + s));
+        }
+    }
+
+    if (METRIC == kNone) return;
+
+    // ---- block reduction, fixed order => deterministic for a given grid ----
+    if (METRIC == kSsd) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    }
+    cnt = warp_sum_u(cnt);
+    if (lane == 0) {
+        s_red[warp] = acc;
+        s_redc[warp] = cnt;
+    }
+    __syncthreads();
+    if (METRIC == kHist) {
+        unsigned *gh = p.d_hist + (size_t)m * p.bins * p.bins;
+        for (int b = tid; b < p.bins * p.bins; b += kTileThreads) {
+            const unsigned c = s_hist[b];
+            if (c) atomicAdd(gh + b, c);
+        }
+    }
+    if (tid == 0) {
+        double sacc = 0.0;
+        unsigned long long c = 0;
+        for (int w = 0; w < kTileThreads / 32; ++w) {
+            sacc += s_red[w];
+            c += s_redc[w];
+        }
+        p.ws_ssd[(size_t)m * gridDim.x + blockIdx.x] = sacc;
+        p.ws_cnt[(size_t)m * gridDim.x + blockIdx.x] = (unsigned)c;
+        __threadfence();
+        const unsigned t = atomicAdd(p.ws_ticket + m, 1u);
+        s_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+
+    // last block of this matrix: fixed-order second stage over all block partials
+    __threadfence();
+    double sacc = 0.0;
+    unsigned long long c = 0;
+    for (unsigned b = tid; b < gridDim.x; b += kTileThreads) {
+        sacc += __ldcg(p.ws_ssd + (size_t)m * gridDim.x + b);
+        c += __ldcg(p.ws_cnt + (size_t)m * gridDim.x + b);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        sacc += __shfl_xor_sync(0xffffffffu, sacc, o);
+        c += __shfl_xor_sync(0xffffffffu, c, o);
+    }
+    __syncthreads();      // s_red / s_redc are reused
+    if (lane == 0) {
+        s_red[warp] = sacc;
+        s_redc[warp] = c;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        double tot = 0.0;
+        unsigned long long tc = 0;
+        for (int w = 0; w < kTileThreads / 32; ++w) {
+            tot += s_red[w];
+            tc += s_redc[w];
+        }
+        if (METRIC == kSsd) p.d_ssd[m] = tot;
+        p.d_count[m] = tc;
+        p.ws_ticket[m] = 0u;     // self-reset: the workspace is reusable without a memset
+    }
+}
+
+}  // namespace mia

@@ -115,7 +115,9 @@ def test_hist_is_order_independent_and_batched_equals_single(cuda_device):
 
 def test_z_slab_partials_sum_to_the_whole(cuda_device):
     """The sharding rule of SURVEY 8e on one GPU: slabs of the fixed lattice, each with its own shifted A,
-    give integer histograms that add up bit for bit and SSD partials that add up to 1e-12."""
+    give integer histograms that add up bit for bit and SSD partials that add up to 1e-8 relative: a slab that
+    does not start on an 8-plane tile boundary splits the thread-local float32 coordinates differently, so the
+    interpolated values differ in their last bits (1000 times below the 1e-5 metric tolerance)."""
     g, fixed, moving, _ = pair(shape=(32, 40, 64), fdtype="CT", mdtype="CT")
     A = mats(g, 1, seed=8)[0]
     f, m = torch.from_numpy(fixed).to(cuda_device), torch.from_numpy(moving).to(cuda_device)
@@ -134,7 +136,7 @@ def test_z_slab_partials_sum_to_the_whole(cuda_device):
         s, _ = kernels.resample_ssd(f[k0:k1].contiguous(), m, A=As)
         ss += float(s[0])
     assert torch.equal(hs[0], hw[0].long()) and cs == int(cw[0])
-    assert abs(ss - sw) <= 1e-12 * sw
+    assert abs(ss - sw) <= 1e-8 * sw
 
 
 def test_metric_error_paths(cuda_device):

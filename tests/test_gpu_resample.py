@@ -26,7 +26,7 @@ def border_band(A, odims, mdims, eps=1e-4):
     return near
 
 
-def check_parity(got, want, near, out_dtype, bg):
+def check_parity(got, want, near, out_dtype, bg, max_near=0.02):
     got = np.asarray(got)
     if np.dtype(out_dtype).kind == "i":
         d = np.abs(got.astype(np.int64) - want.astype(np.int64))
@@ -37,7 +37,7 @@ def check_parity(got, want, near, out_dtype, bg):
     bad &= ~near
     assert not bad.any(), "%d voxels out of tolerance (max |diff| %g)" % (
         bad.sum(), np.abs(got.astype(np.float64) - want.astype(np.float64))[bad].max())
-    assert near.mean() < 0.02
+    assert near.mean() < max_near
 
 
 def run_case(dev, mov, A, odims, mode, out_dtype=None):
@@ -61,7 +61,10 @@ def test_golden_vectors(cuda_device, golden):
                 got = kernels.resample(t, A, (odims[2], odims[1], odims[0]), background=BG[mode], mode=mode)
                 want = golden["%s/%s/%s" % (name, tag, mode)]
                 near = border_band(A, odims, (mov.shape[2], mov.shape[1], mov.shape[0]))
-                check_parity(got.cpu().numpy(), want, near, mov.dtype, BG[mode])
+                # shift_half puts three whole faces exactly on the -0.5 border (bit-exactness of those ties is
+                # asserted in test_exact_cases_are_bit_exact); everywhere else the band must be tiny
+                check_parity(got.cpu().numpy(), want, near, mov.dtype, BG[mode],
+                             max_near=0.2 if name == "shift_half" else 0.02)
 
 
 @pytest.mark.parametrize("name", ["identity", "shift_int", "shift_half"])

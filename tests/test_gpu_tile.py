@@ -1,0 +1,166 @@
+"""Parity of the TMA-staged tile kernel (csrc/mia_tile.cuh) with the oracle, through the C ABI.
+
+The tile path needs a 16-byte aligned moving row pitch, so these cases use x sizes that are multiples of 8;
+``mia_debug_last_path()`` proves which kernel ran.  Tolerances as in test_gpu_resample.py.
+"""
+import numpy as np
+import pytest
+import torch
+
+from medicalimageanalysis_b200 import _lib, geometry as G
+from medicalimageanalysis_b200 import kernels
+from medicalimageanalysis_b200.phantom import make_phantom
+from oracle import metrics, native, reslice
+from tests.test_gpu_resample import BG, border_band, check_parity
+
+pytestmark = pytest.mark.gpu
+TILE, DIRECT = 1, 0
+
+
+def last_path():
+    return int(_lib.load().mia_debug_last_path())
+
+
+def grid_of(shape, sp):
+    return G.Grid((shape[2], shape[1], shape[0]), sp, tuple(-0.5 * np.array(sp) * np.array(shape[::-1])))
+
+
+def run(dev, mov, A, odims, mode, expect=TILE):
+    t = torch.from_numpy(mov).to(dev)
+    got = kernels.resample(t, A, (odims[2], odims[1], odims[0]), background=BG[mode], mode=mode)
+    assert last_path() == expect
+    want = reslice.oracle_reslice(mov, A, odims, BG[mode], mode, mov.dtype)
+    near = border_band(A, odims, (mov.shape[2], mov.shape[1], mov.shape[0]))
+    check_parity(got.cpu().numpy(), want, near, mov.dtype, BG[mode])
+    return got
+
+
+@pytest.mark.parametrize("modality", ["CT", "MR"])
+@pytest.mark.parametrize("seed", range(4))
+def test_tile_random_rigid_parity(cuda_device, modality, seed):
+    rng = np.random.default_rng(300 + seed)
+    shape = (int(rng.integers(9, 60)), int(rng.integers(17, 90)), 8 * int(rng.integers(5, 20)))
+    sp = (float(rng.uniform(0.6, 1.2)),) * 2 + (float(rng.uniform(1.0, 3.0)),)
+    mov = make_phantom(shape, modality, seed=seed, spacing=sp)
+    g = grid_of(shape, sp)
+    p = np.concatenate([rng.uniform(-4, 4, 3), rng.uniform(-8, 8, 3)])
+    A = G.compose_index_matrix(g, g, G.params_to_matrix(p, (0, 0, 0)))
+    for mode in ("vtk", "itk"):
+        run(cuda_device, mov, A, g.dims, mode)
+
+
+def test_tile_autocrop_output_larger_than_moving(cuda_device):
+    """Output lattice sticks out of the moving volume on every side: outside, border and interior tiles."""
+    shape, sp = (40, 64, 96), (0.9765625, 0.9765625, 2.5)
+    mov = make_phantom(shape, "CT", seed=5, spacing=sp)
+    g = grid_of(shape, sp)
+    M = G.params_to_matrix([3, -2, 4, 5, -3, 7], (0, 0, 0))
+    origin, odims = G.autocrop_extent(g, M, sp)
+    og = G.Grid(tuple(int(d) for d in odims), sp, tuple(origin))
+    A = G.compose_index_matrix(og, g, M, "vtk")
+    run(cuda_device, mov, A, og.dims, "vtk")
+    # a much larger canvas: most tiles are entirely outside
+    A2 = A.copy()
+    A2[:, 3] -= A2[:, :3] @ np.array([40.0, 30.0, 10.0])
+    run(cuda_device, mov, A2, (og.dims[0] + 80, og.dims[1] + 60, og.dims[2] + 20), "vtk")
+
+
+@pytest.mark.parametrize("name", ["identity", "shift_int", "shift_half"])
+@pytest.mark.parametrize("tag", ["i16", "f32"])
+def test_tile_exact_cases_bit_exact(cuda_device, name, tag):
+    rng = np.random.default_rng(11)
+    shape = (21, 37, 64)
+    mov = rng.integers(-1024, 3071, size=shape).astype(np.int16 if tag == "i16" else np.float32)
+    A = np.hstack([np.identity(3), np.zeros((3, 1))])
+    if name == "shift_int":
+        A[:, 3] = [3.0, -2.0, 1.0]
+    elif name == "shift_half":
+        A[:, 3] = [0.5, -0.5, 0.5]
+    odims = (64, 37, 21)
+    for mode in ("vtk", "itk"):
+        t = torch.from_numpy(mov).to(cuda_device)
+        got = kernels.resample(t, A, shape, background=BG[mode], mode=mode)
+        assert last_path() == TILE
+        want = reslice.oracle_reslice(mov, A, odims, BG[mode], mode, mov.dtype)
+        assert np.array_equal(got.cpu().numpy(), want), (name, tag, mode)
+
+
+def test_tile_thin_volume_and_ragged_output(cuda_device):
+    """Moving volume thinner than the box; output sizes that are not multiples of the 32x8x8 tile."""
+    rng = np.random.default_rng(12)
+    mov = rng.integers(-500, 1500, size=(3, 5, 16)).astype(np.int16)
+    A = np.hstack([np.identity(3), np.zeros((3, 1))])
+    A[:, 3] = [0.3, -0.2, 0.1]
+    for odims in [(16, 5, 3), (33, 9, 9), (1, 1, 1), (70, 3, 17)]:
+        for mode in ("vtk", "itk"):
+            run(cuda_device, mov, A, odims, mode)
+
+
+def test_large_rotation_host_matrix_goes_direct_and_device_matrix_falls_back_per_tile(cuda_device):
+    shape, sp = (32, 64, 64), (1.0, 1.0, 1.0)
+    fixed = make_phantom(shape, "CT", seed=8, spacing=sp)
+    moving = make_phantom(shape, "CT", seed=9, spacing=sp)
+    g = grid_of(shape, sp)
+    A = G.compose_index_matrix(g, g, G.params_to_matrix([35, -20, 40, 2, 1, -3], (0, 0, 0)))
+    run(cuda_device, moving, A, g.dims, "vtk", expect=DIRECT)
+    f, m = torch.from_numpy(fixed).to(cuda_device), torch.from_numpy(moving).to(cuda_device)
+    s_host, c_host = kernels.resample_ssd(f, m, A=A)
+    assert last_path() == DIRECT
+    dA = torch.from_numpy(np.ascontiguousarray(A[None])).to(cuda_device)
+    s_dev, c_dev = kernels.resample_ssd(f, m, d_A=dA, ws=kernels.MetricWorkspace(cuda_device, n_mats=1))
+    assert last_path() == TILE
+    want, n = native.reslice_ssd(fixed, moving, A, "itk")
+    for s, c in ((s_host, c_host), (s_dev, c_dev)):
+        assert abs(int(c[0]) - n) <= 2
+        assert abs(float(s[0]) - want) <= 1e-5 * want
+
+
+@pytest.mark.parametrize("modality", ["CT", "MR"])
+def test_tile_metrics_match_oracle(cuda_device, modality):
+    shape, sp = (40, 56, 80), (1.0, 1.0, 2.0)
+    g = grid_of(shape, sp)
+    Mgt = G.params_to_matrix([3, -2, 4, 3, -2, 1], (0, 0, 0))
+    fixed = make_phantom(shape, modality, seed=3, spacing=sp)
+    moving = make_phantom(shape, modality, seed=3, spacing=sp, world_matrix=np.linalg.inv(Mgt))
+    rng = np.random.default_rng(5)
+    A = np.stack([G.compose_index_matrix(g, g, G.params_to_matrix(
+        np.concatenate([rng.uniform(-4, 4, 3), rng.uniform(-4, 4, 3)]), (0, 0, 0))) for _ in range(13)])
+    f, m = torch.from_numpy(fixed).to(cuda_device), torch.from_numpy(moving).to(cuda_device)
+    ws = kernels.MetricWorkspace(cuda_device, n_mats=13, bins=64)
+    s, c = kernels.resample_ssd(f, m, A=A, ws=ws)
+    assert last_path() == TILE
+    fr = (float(fixed.min()), float(fixed.max()))
+    mr = (float(moving.min()), float(moving.max()))
+    s, c = s.cpu().numpy().copy(), c.cpu().numpy().copy()
+    h, hc = kernels.resample_jointhist(f, m, fr, mr, bins=64, A=A, ws=ws)
+    assert last_path() == TILE
+    mi = kernels.mi_from_hist(h).cpu().numpy()
+    h, hc = h.cpu().numpy(), hc.cpu().numpy()
+    for i in range(13):
+        want, n = native.reslice_ssd(fixed, moving, A[i], "itk")
+        assert abs(int(c[i]) - n) <= 2
+        assert abs(float(s[i]) - want) <= 1e-5 * want
+        H = native.joint_hist(fixed, moving, A[i], 64, fr, mr, "itk")[0]
+        assert abs(int(hc[i]) - int(H.sum())) <= 2 and int(h[i].sum()) == int(hc[i])
+        # float32 vs float64 interpolation may move a handful of samples across a bin edge
+        assert np.abs(h[i].astype(np.int64) - H.astype(np.int64)).sum() <= max(8, 2e-5 * H.sum())
+        want_mi = metrics.oracle_mi(H)
+        assert abs(mi[i] - want_mi) <= 1e-5 * abs(want_mi)
+
+
+def test_tile_ssd_store_equals_plain_resample_and_is_deterministic(cuda_device):
+    shape, sp = (24, 48, 72), (1.0, 1.0, 2.0)
+    g = grid_of(shape, sp)
+    fixed = make_phantom(shape, "CT", seed=3, spacing=sp)
+    moving = make_phantom(shape, "CT", seed=4, spacing=sp)
+    A = G.compose_index_matrix(g, g, G.params_to_matrix([2, 1, -3, 1, -2, 2], (0, 0, 0)))
+    f, m = torch.from_numpy(fixed).to(cuda_device), torch.from_numpy(moving).to(cuda_device)
+    out = torch.empty_like(m)
+    s, c = kernels.resample_ssd(f, m, A=A, mode="itk", out=out, background=0.0)
+    assert last_path() == TILE
+    s0 = float(s[0])
+    plain = kernels.resample(m, A, m.shape, background=0.0, mode="itk")
+    assert torch.equal(out, plain)
+    for _ in range(3):
+        s2, _ = kernels.resample_ssd(f, m, A=A, mode="itk")
+        assert float(s2[0]) == s0
