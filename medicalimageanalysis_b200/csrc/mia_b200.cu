@@ -131,9 +131,9 @@ void dispatch_metric(int mov_dtype, int fixed_dtype, const KParams &p, int mode,
 thread_local int g_last_path = 0;    // 0 = direct kernel, 1 = tile kernel (diagnostic, mia_debug_last_path)
 
 template <typename TM> struct BoxFor;
-template <> struct BoxFor<int16_t> { using type = Box<48, 18, 16>; };
+template <> struct BoxFor<int16_t> { using type = Box<64, 16, 12>; };   // 64 shorts = 32 words: row pitch = 0 mod 32 banks
 template <> struct BoxFor<float>   { using type = Box<40, 18, 14>; };
-constexpr int kTileStages = 2;
+template <typename TM> struct StagesFor { static constexpr int value = sizeof(TM) == 2 ? 3 : 2; };
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
@@ -206,8 +206,9 @@ int launch_tile(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream
 {
     using BOX = typename BoxFor<TM>::type;
     constexpr int MINB = sizeof(TM) == 2 ? 3 : 2;
-    auto k = tile_kernel<TM, TF, TO, METRIC, STORE, VTK, BOX, kTileStages, MINB>;
-    const size_t smem = TileSmem<TM, BOX, kTileStages>::bytes(METRIC == kHist ? p.bins : 0);
+    constexpr int NST = StagesFor<TM>::value;
+    auto k = tile_kernel<TM, TF, TO, METRIC, STORE, VTK, BOX, NST, MINB>;
+    const size_t smem = TileSmem<TM, BOX, NST>::bytes(METRIC == kHist ? p.bins : 0);
     static std::mutex mu;
     static std::map<std::pair<int, size_t>, int> occ;     // (device, smem) -> resident CTAs per SM
     int dev = 0;

@@ -33,7 +33,7 @@ struct Box {
 };
 
 struct TileInfo {          // producer -> consumers, one per ring stage
-    double c0x, c0y, c0z;  // continuous moving index of the tile's first voxel
+    long long rx, ry, rz;  // (continuous moving index of the tile's first voxel - box origin) in Q31.32 fixed point
     int bx, by, bz;        // moving index of box element [0][0][0]
     int cls;
 };
@@ -145,7 +145,6 @@ __host__ __device__ inline TileInfo classify_tile(const double *A, const Reach &
     const double c0[3] = {((A[3] + (double)k0 * A[2]) + (double)j0 * A[1]) + (double)i0 * A[0],
                           ((A[7] + (double)k0 * A[6]) + (double)j0 * A[5]) + (double)i0 * A[4],
                           ((A[11] + (double)k0 * A[10]) + (double)j0 * A[9]) + (double)i0 * A[8]};
-    t.c0x = c0[0]; t.c0y = c0[1]; t.c0z = c0[2];
     const int n[3] = {nx, ny, nz};
     const int B[3] = {BOX::kX, BOX::kY, BOX::kZ};
     int b[3] = {0, 0, 0};
@@ -166,6 +165,12 @@ __host__ __device__ inline TileInfo classify_tile(const double *A, const Reach &
     }
     t.bx = b[0]; t.by = b[1]; t.bz = b[2];
     t.cls = outside ? kOutside : (!fits ? kNoFit : (interior ? kInterior : kBorder));
+    t.rx = t.ry = t.rz = 0;
+    if (t.cls == kInterior || t.cls == kBorder) {       // |c0 - b| is a few box widths at most here
+        t.rx = (long long)floor((c0[0] - (double)b[0]) * 4294967296.0);
+        t.ry = (long long)floor((c0[1] - (double)b[1]) * 4294967296.0);
+        t.rz = (long long)floor((c0[2] - (double)b[2]) * 4294967296.0);
+    }
     return t;
 }
 
@@ -206,28 +211,82 @@ struct Tap<float, BYTE_OFF> {
 __device__ __forceinline__ void st_out(int16_t *p, int16_t v) { asm volatile("st.global.cs.u16 [%0], %1;" ::"l"(p), "h"(v) : "memory"); }
 __device__ __forceinline__ void st_out(float *p, float v) { asm volatile("st.global.cs.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory"); }
 
+// ---- packed float32x2 arithmetic (Blackwell FADD2 / FFMA2): one issue slot for two voxels ------------
+// The kernel is issue-bound, not FP32-pipe bound (ncu: 71 % issue slots, 31 % FMA pipe), so the z-adjacent
+// voxel pair (kz, kz+1) of a thread shares every coordinate and lerp instruction.
+typedef unsigned long long f32x2;
+
+__device__ __forceinline__ f32x2 pk(float lo, float hi)
+{
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void upk(f32x2 v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c)
+{
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b)
+{
+    f32x2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b)
+{
+    f32x2 r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 add2_rm(f32x2 a, f32x2 b)
+{
+    f32x2 r;
+    asm("add.rm.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 lerp2(f32x2 w, f32x2 a, f32x2 b) { return fma2(w, sub2(b, a), a); }
+
+// Per-thread constants of a launch: (lane * A[:,0] + warp * A[:,1]) in Q31.32 and the z column in float32.
+struct ThreadGeom {
+    long long ox, oy, oz;
+    float a2x, a2y, a2z;
+};
+
+__device__ __forceinline__ ThreadGeom make_thread_geom(const double *A, int lane, int warp)
+{
+    ThreadGeom g;
+    g.ox = __double2ll_rn(((double)lane * A[0] + (double)warp * A[1]) * 4294967296.0);
+    g.oy = __double2ll_rn(((double)lane * A[4] + (double)warp * A[5]) * 4294967296.0);
+    g.oz = __double2ll_rn(((double)lane * A[8] + (double)warp * A[9]) * 4294967296.0);
+    g.a2x = (float)A[2]; g.a2y = (float)A[6]; g.a2z = (float)A[10];
+    return g;
+}
+
 // One consumer thread's share of one tile whose box is resident in shared memory: the 8 z planes of
-// output voxel column (i0 + lane, j0 + warp).  BORDER adds the inside test and the coordinate clamp
-// (== VTK/ITK index clamp: the clamped coordinate has weight 0 on the tap beyond the edge, which TMA
-// zero-filled); interior tiles need neither.
+// output voxel column (i0 + lane, j0 + warp), as 4 packed pairs.  BORDER adds the inside test and the
+// coordinate clamp (== VTK/ITK index clamp: the clamped coordinate has weight 0 on the tap beyond the edge,
+// which TMA zero-filled); interior tiles need neither.
 template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, bool BORDER, class BOX>
 __device__ __forceinline__ void tile_compute(const KParams &p, const unsigned char *stage, const TileInfo &ti,
-                                             const double *A, int i0, int j0, int k0, int lane, int warp,
+                                             const ThreadGeom &g, int i0, int j0, int k0, int lane, int warp,
                                              double &acc, unsigned &cnt, unsigned *s_hist)
 {
+    static_assert(kTZ % 2 == 0, "voxels are processed in z pairs");
     constexpr unsigned ES = sizeof(TM);
     constexpr int PY = BOX::kX * ES, PZ = BOX::kX * BOX::kY * ES;
     const int i = i0 + lane, j = j0 + warp;
     const bool row_ok = (i < p.ox) & (j < p.oy);
     const int kcnt = min(kTZ, p.oz - k0);
 
-    // thread base in float64, split into an integer box offset and a float32 fraction
-    const double rx = fma((double)lane, A[0], fma((double)warp, A[1], ti.c0x)) - (double)ti.bx;
-    const double ry = fma((double)lane, A[4], fma((double)warp, A[5], ti.c0y)) - (double)ti.by;
-    const double rz = fma((double)lane, A[8], fma((double)warp, A[9], ti.c0z)) - (double)ti.bz;
-    const int tbx = __double2int_rd(rx), tby = __double2int_rd(ry), tbz = __double2int_rd(rz);
-    const float fx = (float)(rx - (double)tbx), fy = (float)(ry - (double)tby), fz = (float)(rz - (double)tbz);
-    const float a2x = (float)A[2], a2y = (float)A[6], a2z = (float)A[10];
+    // thread base: 64-bit fixed point add, integer part = box element, top 24 fraction bits -> float32
+    const long long tx64 = ti.rx + g.ox, ty64 = ti.ry + g.oy, tz64 = ti.rz + g.oz;
+    const int tbx = (int)(tx64 >> 32), tby = (int)(ty64 >> 32), tbz = (int)(tz64 >> 32);
+    const float fx = (float)((unsigned)tx64 >> 8) * 5.9604644775390625e-8f;
+    const float fy = (float)((unsigned)ty64 >> 8) * 5.9604644775390625e-8f;
+    const float fz = (float)((unsigned)tz64 >> 8) * 5.9604644775390625e-8f;
     // element index = ((iz*BY + iy)*BX + ix) with i* = thread base + floor(local); floor(local) arrives as the
     // raw bits of (local + kMagic), i.e. kMagicBits + floor: the constant part is folded into ubase (mod 2^32)
     const uint32_t ubase = smem_u32(stage) +
@@ -259,54 +318,76 @@ __device__ __forceinline__ void tile_compute(const KParams &p, const unsigned ch
             fv[kz] = (row_ok && kz < kcnt) ? (float)__ldg(fixed + (unsigned)kz * plane) : 0.0f;
     }
 
-    float part = 0.0f;
+    const f32x2 ax2 = pk(g.a2x, g.a2x), ay2 = pk(g.a2y, g.a2y), az2 = pk(g.a2z, g.a2z);
+    const f32x2 fx2 = pk(fx, fx), fy2 = pk(fy, fy), fz2 = pk(fz, fz);
+    const f32x2 magic2 = pk(kMagic, kMagic);
+    f32x2 part2 = pk(0.0f, 0.0f);
 #pragma unroll
-    for (int kz = 0; kz < kTZ; ++kz) {
-        float lx = fmaf((float)kz, a2x, fx), ly = fmaf((float)kz, a2y, fy), lz = fmaf((float)kz, a2z, fz);
-        bool in = true;
+    for (int kp = 0; kp < kTZ; kp += 2) {
+        const f32x2 kk = pk((float)kp, (float)(kp + 1));
+        f32x2 lx2 = fma2(kk, ax2, fx2), ly2 = fma2(kk, ay2, fy2), lz2 = fma2(kk, az2, fz2);
+        bool in0 = true, in1 = true;
         if (BORDER) {
-            in = (lx >= ilox) & (lx <= ihix) & (ly >= iloy) & (ly <= ihiy) & (lz >= iloz) & (lz <= ihiz);
-            lx = fminf(fmaxf(lx, clox), chix);
-            ly = fminf(fmaxf(ly, cloy), chiy);
-            lz = fminf(fmaxf(lz, cloz), chiz);
+            float x0, x1, y0, y1, z0, z1;
+            upk(lx2, x0, x1); upk(ly2, y0, y1); upk(lz2, z0, z1);
+            in0 = (x0 >= ilox) & (x0 <= ihix) & (y0 >= iloy) & (y0 <= ihiy) & (z0 >= iloz) & (z0 <= ihiz);
+            in1 = (x1 >= ilox) & (x1 <= ihix) & (y1 >= iloy) & (y1 <= ihiy) & (z1 >= iloz) & (z1 <= ihiz);
+            lx2 = pk(fminf(fmaxf(x0, clox), chix), fminf(fmaxf(x1, clox), chix));
+            ly2 = pk(fminf(fmaxf(y0, cloy), chiy), fminf(fmaxf(y1, cloy), chiy));
+            lz2 = pk(fminf(fmaxf(z0, cloz), chiz), fminf(fmaxf(z1, cloz), chiz));
         }
-        const float tx = add_rm(lx, kMagic), ty = add_rm(ly, kMagic), tz = add_rm(lz, kMagic);
-        const float wx = lx - (tx - kMagic), wy = ly - (ty - kMagic), wz = lz - (tz - kMagic);
-        const uint32_t a = ((__float_as_uint(tz) * BOX::kY + __float_as_uint(ty)) * BOX::kX + __float_as_uint(tx)) * ES + ubase;
-        const float v000 = Tap<TM, 0>::ld(a), v100 = Tap<TM, ES>::ld(a);
-        const float v010 = Tap<TM, PY>::ld(a), v110 = Tap<TM, PY + ES>::ld(a);
-        const float v001 = Tap<TM, PZ>::ld(a), v101 = Tap<TM, PZ + ES>::ld(a);
-        const float v011 = Tap<TM, PZ + PY>::ld(a), v111 = Tap<TM, PZ + PY + ES>::ld(a);
-        const float vx00 = fmaf(wx, v100 - v000, v000);
-        const float vx10 = fmaf(wx, v110 - v010, v010);
-        const float vx01 = fmaf(wx, v101 - v001, v001);
-        const float vx11 = fmaf(wx, v111 - v011, v011);
-        const float vxx0 = fmaf(wy, vx10 - vx00, vx00);
-        const float vxx1 = fmaf(wy, vx11 - vx01, vx01);
-        const float val = fmaf(wz, vxx1 - vxx0, vxx0);
-        const bool live = row_ok && kz < kcnt;
+        const f32x2 tx2 = add2_rm(lx2, magic2), ty2 = add2_rm(ly2, magic2), tz2 = add2_rm(lz2, magic2);
+        const f32x2 wx2 = sub2(lx2, sub2(tx2, magic2)), wy2 = sub2(ly2, sub2(ty2, magic2)), wz2 = sub2(lz2, sub2(tz2, magic2));
+        const uint32_t txa = (uint32_t)tx2, txb = (uint32_t)(tx2 >> 32);
+        const uint32_t tya = (uint32_t)ty2, tyb = (uint32_t)(ty2 >> 32);
+        const uint32_t tza = (uint32_t)tz2, tzb = (uint32_t)(tz2 >> 32);
+        const uint32_t a0 = ((tza * BOX::kY + tya) * BOX::kX + txa) * ES + ubase;
+        const uint32_t a1 = ((tzb * BOX::kY + tyb) * BOX::kX + txb) * ES + ubase;
+        const f32x2 v000 = pk(Tap<TM, 0>::ld(a0), Tap<TM, 0>::ld(a1));
+        const f32x2 v100 = pk(Tap<TM, ES>::ld(a0), Tap<TM, ES>::ld(a1));
+        const f32x2 v010 = pk(Tap<TM, PY>::ld(a0), Tap<TM, PY>::ld(a1));
+        const f32x2 v110 = pk(Tap<TM, PY + ES>::ld(a0), Tap<TM, PY + ES>::ld(a1));
+        const f32x2 v001 = pk(Tap<TM, PZ>::ld(a0), Tap<TM, PZ>::ld(a1));
+        const f32x2 v101 = pk(Tap<TM, PZ + ES>::ld(a0), Tap<TM, PZ + ES>::ld(a1));
+        const f32x2 v011 = pk(Tap<TM, PZ + PY>::ld(a0), Tap<TM, PZ + PY>::ld(a1));
+        const f32x2 v111 = pk(Tap<TM, PZ + PY + ES>::ld(a0), Tap<TM, PZ + PY + ES>::ld(a1));
+        const f32x2 vx00 = lerp2(wx2, v000, v100), vx10 = lerp2(wx2, v010, v110);
+        const f32x2 vx01 = lerp2(wx2, v001, v101), vx11 = lerp2(wx2, v011, v111);
+        const f32x2 vxx0 = lerp2(wy2, vx00, vx10), vxx1 = lerp2(wy2, vx01, vx11);
+        const f32x2 val2 = lerp2(wz2, vxx0, vxx1);
+        float val0, val1;
+        upk(val2, val0, val1);
+        const bool live0 = row_ok && kp < kcnt, live1 = row_ok && kp + 1 < kcnt;
         if (STORE) {
-            const TO o = tile_to_out<TO, VTK>(val);
-            const TO r = in ? o : bgv;
-            if (live) st_out(out + (unsigned)kz * plane, r);
+            const TO o0 = tile_to_out<TO, VTK>(val0), o1 = tile_to_out<TO, VTK>(val1);
+            if (live0) st_out(out + (unsigned)kp * plane, in0 ? o0 : bgv);
+            if (live1) st_out(out + (unsigned)(kp + 1) * plane, in1 ? o1 : bgv);
         }
         if (METRIC == kSsd) {
-            const float d = fv[kz] - val;
-            if (live && in) {
-                part = fmaf(d, d, part);
-                ++cnt;
-            }
+            f32x2 d2 = sub2(pk(fv[kp], fv[kp + 1]), val2);
+            float d0, d1;
+            upk(d2, d0, d1);
+            const bool u0 = live0 && in0, u1 = live1 && in1;
+            d2 = pk(u0 ? d0 : 0.0f, u1 ? d1 : 0.0f);
+            part2 = fma2(d2, d2, part2);
+            cnt += (u0 ? 1u : 0u) + (u1 ? 1u : 0u);
         }
         if (METRIC == kHist) {
-            if (live && in) {
-                const int bf = bin_of(fv[kz], p.fmin, p.fscale, p.bins);
-                const int bm = bin_of(val, p.mmin, p.mscale, p.bins);
-                atomicAdd(&s_hist[bf * p.bins + bm], 1u);
+            if (live0 && in0) {
+                atomicAdd(&s_hist[bin_of(fv[kp], p.fmin, p.fscale, p.bins) * p.bins + bin_of(val0, p.mmin, p.mscale, p.bins)], 1u);
+                ++cnt;
+            }
+            if (live1 && in1) {
+                atomicAdd(&s_hist[bin_of(fv[kp + 1], p.fmin, p.fscale, p.bins) * p.bins + bin_of(val1, p.mmin, p.mscale, p.bins)], 1u);
                 ++cnt;
             }
         }
     }
-    if (METRIC == kSsd) acc += (double)part;
+    if (METRIC == kSsd) {
+        float s0, s1;
+        upk(part2, s0, s1);
+        acc += (double)(s0 + s1);
+    }
 }
 
 // Tiles that need no box: entirely outside (background only) or too large for the box (per-voxel global
@@ -356,13 +437,13 @@ struct TileSmem {
     static constexpr unsigned kStageBytes = (kBoxBytes + 127u) & ~127u;
     static constexpr unsigned kBarOff = kStageBytes * NST;
     static constexpr unsigned kInfoOff = kBarOff + 16u * NST;
-    static constexpr unsigned kHistOff = (kInfoOff + (unsigned)sizeof(TileInfo) * NST + 15u) & ~15u;
+    static constexpr unsigned kHistOff = (kInfoOff + (unsigned)sizeof(TileInfo) * 64u + 15u) & ~15u;
     static size_t bytes(int bins) { return (size_t)kHistOff + sizeof(unsigned) * (size_t)bins * bins; }
 };
 
 template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, class BOX, int NST, int MINB>
 __global__ void __launch_bounds__(kTileThreads, MINB)
-tile_kernel(const __grid_constant__ CUtensorMap tmap, const KParams p)
+tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ KParams p)
 {
     using L = TileSmem<TM, BOX, NST>;
     extern __shared__ __align__(1024) unsigned char tsm[];
@@ -397,49 +478,81 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const KParams p)
     double acc = 0.0;
     unsigned cnt = 0;
 
+    // tiles are visited as tile = blockIdx.x + n * gridDim.x; (tix, tiy, tiz) advance incrementally
+    const int txy = p.ntx * p.nty;
+    const int step_z = (int)(gridDim.x / (unsigned)txy), step_r = (int)(gridDim.x % (unsigned)txy);
+    const int step_y = step_r / p.ntx, step_x = step_r % p.ntx;
+    int tiz = (int)(blockIdx.x / (unsigned)txy);
+    int tiy = (int)(blockIdx.x % (unsigned)txy) / p.ntx, tix = (int)(blockIdx.x % (unsigned)txy) % p.ntx;
+    const int ntile_mine = (int)((p.ntiles - 1 - blockIdx.x) / gridDim.x) + 1;
+    auto advance = [&]() {
+        tix += step_x;
+        if (tix >= p.ntx) { tix -= p.ntx; ++tiy; }
+        tiy += step_y;
+        if (tiy >= p.nty) { tiy -= p.nty; ++tiz; }
+        tiz += step_z;
+    };
+
     if (warp == kConsumerWarps) {
-        // ---------------- producer: one lane ----------------
-        if (lane == 0) {
-            const Reach reach = tile_reach(A);
-            unsigned n = 0;
-            for (long long tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++n) {
-                const unsigned s = n % NST, ph = (n / NST) & 1u;
-                mbar_wait(bar0 + 8 * (NST + s), ph ^ 1u);
-                const int tix = (int)(tile % p.ntx);
-                const long long t2 = tile / p.ntx;
-                const int tiy = (int)(t2 % p.nty), tiz = (int)(t2 / p.nty);
-                const TileInfo ti = classify_tile<BOX>(A, reach, tix * kTX, tiy * kTY, tiz * kTZ, p.mov.nx, p.mov.ny, p.mov.nz,
-                                                            16 / (int)sizeof(TM));
-                infos[s] = ti;
-                if (ti.cls == kInterior || ti.cls == kBorder) {
-                    mbar_arrive_expect_tx(bar0 + 8 * s, L::kBoxBytes);
-                    tma_load_3d(smem_u32(tsm + L::kStageBytes * s), &tmap, bar0 + 8 * s, ti.bx, ti.by, ti.bz);
-                } else {
-                    mbar_arrive(bar0 + 8 * s);
-                }
+        // ---------------- producer warp ----------------
+        // Classification is SIMD over the warp: in one pass lane q classifies this CTA's tile number base + q,
+        // so the float64 chain is paid once per 32 tiles and never sits on the critical path of a TMA issue.
+        // The records go to a 64-entry queue (two passes deep); lane 0 then feeds the stage ring.
+        const Reach reach = tile_reach(A);
+        unsigned s = 0, ph = 0;
+        for (int base = 0; base < ntile_mine; base += 32) {
+            const int n = base + lane;
+            TileInfo mine;
+            mine.rx = mine.ry = mine.rz = 0;
+            mine.bx = mine.by = mine.bz = 0;
+            mine.cls = kOutside;
+            if (n < ntile_mine) {
+                const unsigned tile = blockIdx.x + (unsigned)n * gridDim.x;
+                const int z = (int)(tile / (unsigned)txy), r2 = (int)(tile % (unsigned)txy);
+                mine = classify_tile<BOX>(A, reach, (r2 % p.ntx) * kTX, (r2 / p.ntx) * kTY, z * kTZ, p.mov.nx, p.mov.ny, p.mov.nz,
+                                          16 / (int)sizeof(TM));
             }
+            infos[(base & 32) + lane] = mine;
+            __syncwarp();
+            const int cnt_pass = min(32, ntile_mine - base);
+            for (int q = 0; q < cnt_pass; ++q) {
+                const int cls = __shfl_sync(0xffffffffu, mine.cls, q);
+                const int bx = __shfl_sync(0xffffffffu, mine.bx, q);
+                const int by = __shfl_sync(0xffffffffu, mine.by, q);
+                const int bz = __shfl_sync(0xffffffffu, mine.bz, q);
+                if (lane == 0) {
+                    mbar_wait(bar0 + 8 * (NST + s), ph ^ 1u);
+                    if (cls == kInterior || cls == kBorder) {
+                        mbar_arrive_expect_tx(bar0 + 8 * s, L::kBoxBytes);
+                        tma_load_3d(smem_u32(tsm + L::kStageBytes * s), &tmap, bar0 + 8 * s, bx, by, bz);
+                    } else {
+                        mbar_arrive(bar0 + 8 * s);
+                    }
+                }
+                if (++s == NST) { s = 0; ph ^= 1u; }
+            }
+            __syncwarp();
         }
     } else {
         // ---------------- consumers: 8 warps ----------------
-        unsigned n = 0;
-        for (long long tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++n) {
-            const unsigned s = n % NST, ph = (n / NST) & 1u;
-            const int tix = (int)(tile % p.ntx);
-            const long long t2 = tile / p.ntx;
-            const int tiy = (int)(t2 % p.nty), tiz = (int)(t2 / p.nty);
+        const ThreadGeom geom = make_thread_geom(A, lane, warp);
+        unsigned s = 0, ph = 0;
+        for (int n = 0; n < ntile_mine; ++n) {
             const int i0 = tix * kTX, j0 = tiy * kTY, k0 = tiz * kTZ;
             mbar_wait(bar0 + 8 * s, ph);
-            const TileInfo ti = infos[s];
+            const TileInfo ti = infos[n & 63];
             const unsigned char *stage = tsm + L::kStageBytes * s;
             if (ti.cls == kInterior)
-                tile_compute<TM, TF, TO, METRIC, STORE, VTK, false, BOX>(p, stage, ti, A, i0, j0, k0, lane, warp, acc, cnt, s_hist);
+                tile_compute<TM, TF, TO, METRIC, STORE, VTK, false, BOX>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt, s_hist);
             else if (ti.cls == kBorder)
-                tile_compute<TM, TF, TO, METRIC, STORE, VTK, true, BOX>(p, stage, ti, A, i0, j0, k0, lane, warp, acc, cnt, s_hist);
+                tile_compute<TM, TF, TO, METRIC, STORE, VTK, true, BOX>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt, s_hist);
             else if (STORE || ti.cls == kNoFit)
                 tile_compute_nobox<TM, TF, TO, METRIC, STORE, VTK>(p, p.dA ? p.dA + 12 * m : p.A0.a, ti.cls, i0, j0, k0, lane, warp,
                                                                    acc, cnt, s_hist);
             __syncwarp();
             if (lane == 0) mbar_arrive(bar0 + 8 * (NST + s));
+            advance();
+            if (++s == NST) { s = 0; ph ^= 1u; }
         }
     }
 
