@@ -10,7 +10,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmia_b200.so")
+LIB_PATH = os.environ.get("MIA_B200_LIB") or os.path.join(_HERE, "libmia_b200.so")   # env override: tuning builds
 
 MIA_I16, MIA_F32 = 0, 1
 MIA_MODE_VTK, MIA_MODE_ITK = 0, 1

@@ -131,9 +131,17 @@ void dispatch_metric(int mov_dtype, int fixed_dtype, const KParams &p, int mode,
 thread_local int g_last_path = 0;    // 0 = direct kernel, 1 = tile kernel (diagnostic, mia_debug_last_path)
 
 template <typename TM> struct BoxFor;
-template <> struct BoxFor<int16_t> { using type = Box<64, 16, 12>; };   // 64 shorts = 32 words: row pitch = 0 mod 32 banks
+#ifndef MIA_BX_I16        // tuning builds override these with -D (see scripts/tune_variants.sh)
+#define MIA_BX_I16 64
+#define MIA_BY_I16 16
+#define MIA_BZ_I16 12
+#endif
+#ifndef MIA_NST_I16
+#define MIA_NST_I16 2
+#endif
+template <> struct BoxFor<int16_t> { using type = Box<MIA_BX_I16, MIA_BY_I16, MIA_BZ_I16>; };   // 64 shorts = 32 words: row pitch = 0 mod 32 banks
 template <> struct BoxFor<float>   { using type = Box<40, 18, 14>; };
-template <typename TM> struct StagesFor { static constexpr int value = sizeof(TM) == 2 ? 3 : 2; };
+template <typename TM> struct StagesFor { static constexpr int value = sizeof(TM) == 2 ? MIA_NST_I16 : 2; };
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,

@@ -18,7 +18,7 @@ __global__ void k_mbar(int *out)
     }
     __syncthreads();
     if (threadIdx.x == 0) mbar_arrive(b);
-    mbar_wait(b, 0);
+    mbar_wait<20>(b, 0);
     out[threadIdx.x] = threadIdx.x;
 }
 
@@ -37,7 +37,7 @@ __global__ void k_tma(const __grid_constant__ CUtensorMap map, short *out, int x
         mbar_arrive_expect_tx(b, nelem * 2);
         tma_load_3d(smem_u32(sm), &map, b, x, y, z);
     }
-    mbar_wait(b, 0);
+    mbar_wait<20>(b, 0);
     const short *s = reinterpret_cast<const short *>(sm);
     for (int i = threadIdx.x; i < nelem; i += blockDim.x) out[i] = s[i];
 }
@@ -72,7 +72,7 @@ __global__ void k_tma_g(const CUtensorMap *map, short *out, int x, int y, int z,
         mbar_arrive_expect_tx(b, nelem * 2);
         tma_load_3d(smem_u32(sm), map, b, x, y, z);
     }
-    mbar_wait(b, 0);
+    mbar_wait<20>(b, 0);
     const short *s = reinterpret_cast<const short *>(sm);
     for (int i = threadIdx.x; i < nelem; i += blockDim.x) out[i] = s[i];
 }
@@ -93,7 +93,7 @@ __global__ void k_bulk(const short *src, short *out, int bytes)
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                      ::"r"(smem_u32(sm)), "l"(src), "r"(bytes), "r"(b) : "memory");
     }
-    mbar_wait(b, 0);
+    mbar_wait<20>(b, 0);
     const short *s = reinterpret_cast<const short *>(sm);
     for (int i = threadIdx.x; i < bytes / 2; i += blockDim.x) out[i] = s[i];
 }
