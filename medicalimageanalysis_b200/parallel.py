@@ -1,0 +1,199 @@
+"""z-slab sharding of the fixed lattice across the GPUs of one box.
+
+The path shards naturally: output / fixed voxels are independent and the metric is one tiny reduction.
+Rank r owns the z-slab ``[k0_r, k1_r)`` of the fixed lattice (boundaries on multiples of the kernel's
+8-plane tile so every rank runs whole tiles), evaluates it with the matrix shifted by its first plane,
+``A[:, 3] += A[:, 2] * k0`` -- the rule ``mia_resample_rigid_host`` uses for its own z-slab pipeline --
+and the partial ``{ssd, count}`` or joint histograms are combined by ``all_reduce(SUM)`` over NCCL / NVLink
+(``gloo`` in the CPU tests).  The moving volume is replicated: ``A`` changes every iteration of a
+registration loop, and even config 5 (2.5 GB) is small next to 180 GB of HBM.
+
+Pure resampling needs no collective at all: the output stays sharded (``resample_slab``), or whole
+volumes are dealt out per rank (config 4, ``bench.py --gpus N``).
+
+The reference has nothing distributed; the call sites this serves are the registration loop of
+``registration.py`` and ``Rigid.create_image`` (``structure/rigid.py:646-695``) on volumes
+too large or too many for one GPU.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+
+from . import geometry as G
+
+TILE_Z = 8      # csrc/mia_tile.cuh kTZ: slab boundaries on tile boundaries keep every tile whole
+
+
+def slab_bounds(nz: int, world: int, align: int = TILE_Z):
+    """``world + 1`` increasing plane indices; slab r is ``[b[r], b[r+1])``.  Interior boundaries are
+    multiples of ``align``; trailing ranks may get an empty slab when there are fewer tiles than ranks."""
+    nz, world = int(nz), int(world)
+    if nz < 0 or world < 1:
+        raise ValueError("need nz >= 0 and world >= 1")
+    ntile = (nz + align - 1) // align
+    b = [min(nz, align * ((ntile * r) // world)) for r in range(world)]
+    return b + [nz]
+
+
+def slab_of(nz: int, rank: int, world: int, align: int = TILE_Z):
+    b = slab_bounds(nz, world, align)
+    return b[rank], b[rank + 1]
+
+
+def shift_matrix(A, k0):
+    """Index matrix of the slab that starts at fixed plane ``k0`` (works on ``[3,4]`` or ``[n,3,4]``,
+    NumPy arrays or torch tensors; returns a new object)."""
+    out = A.clone() if hasattr(A, "clone") else np.array(A, dtype=np.float64, copy=True)
+    out[..., 3] = out[..., 3] + out[..., 2] * float(k0)
+    return out
+
+
+def _dist():
+    import torch.distributed as dist
+    return dist
+
+
+def all_reduce_sum(*tensors, group=None):
+    """In-place SUM over the process group (no-op when torch.distributed is not initialised)."""
+    dist = _dist()
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return tensors
+    for t in tensors:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    return tensors
+
+
+def sharded_ssd(evaluate_slab, nz, A, rank, world, group=None):
+    """Generic driver, also used by the CPU tests with the oracle as ``evaluate_slab``:
+    ``evaluate_slab(k0, k1, A_shifted) -> (ssd[n] float64 tensor, count[n] int64 tensor)`` on this rank's
+    slab; returns the all-reduced pair."""
+    import torch
+    k0, k1 = slab_of(nz, rank, world)
+    n = 1 if np.ndim(A) == 2 else len(A)
+    if k1 > k0:
+        ssd, cnt = evaluate_slab(k0, k1, shift_matrix(A, k0))
+        ssd, cnt = ssd.clone(), cnt.clone()
+    else:
+        ssd, cnt = torch.zeros(n, dtype=torch.float64), torch.zeros(n, dtype=torch.int64)
+    all_reduce_sum(ssd, cnt, group=group)
+    return ssd, cnt
+
+
+def sharded_hist(evaluate_slab, nz, A, bins, rank, world, group=None):
+    """Same for joint histograms: ``evaluate_slab(k0, k1, A_shifted) -> (hist[n,B,B] int, count[n] int64)``.
+    Integer sums commute, so the result is bit-identical for every world size."""
+    import torch
+    k0, k1 = slab_of(nz, rank, world)
+    n = 1 if np.ndim(A) == 2 else len(A)
+    if k1 > k0:
+        h, cnt = evaluate_slab(k0, k1, shift_matrix(A, k0))
+        h, cnt = h.to(torch.int64).clone(), cnt.clone()
+    else:
+        h, cnt = torch.zeros((n, bins, bins), dtype=torch.int64), torch.zeros(n, dtype=torch.int64)
+    all_reduce_sum(h, cnt, group=group)
+    return h, cnt
+
+
+def resample_slab(moving, A, out_shape, rank, world, background=-3001.0, mode="vtk"):
+    """This rank's z-slab of a resample (no collective).  Returns ``(tensor [k1-k0, y, x], (k0, k1))``."""
+    from . import kernels
+    k0, k1 = slab_of(out_shape[0], rank, world)
+    if k1 <= k0:
+        return None, (k0, k1)
+    out = kernels.resample(moving, shift_matrix(np.asarray(A, dtype=np.float64), k0),
+                           (k1 - k0, out_shape[1], out_shape[2]), background=background, mode=mode)
+    return out, (k0, k1)
+
+
+def register_rigid_sharded(fixed, moving, params0=None, cfg=None, group=None):
+    """``registration.register_rigid`` with the fixed lattice cut into z-slabs over the ranks of ``group``.
+
+    Every rank passes the same ``fixed`` / ``moving`` images (CUDA arrays on its own device; only this rank's
+    slab of ``fixed.array`` is read).  Per iteration: one fused 13-probe launch on the slab, one
+    ``all_reduce`` of ``{ssd[13], count[13]}`` (208 B) or of the 13 joint histograms (13*B*B*4 B), then the
+    one-thread optimiser kernel -- which sees identical sums on every rank, so all ranks walk the same
+    trajectory without exchanging parameters.  Returns the same ``RegistrationResult`` on every rank."""
+    import torch
+
+    from . import _lib, kernels
+    from .registration import N_PROBES, RegistrationConfig, RegistrationResult, _intensity_range
+    dist = _dist()
+    lib = _lib.load()
+    cfg = cfg or RegistrationConfig()
+    on = dist.is_available() and dist.is_initialized()
+    rank = dist.get_rank(group) if on else 0
+    world = dist.get_world_size(group) if on else 1
+    params0 = np.zeros(6) if params0 is None else np.asarray(params0, dtype=np.float64)
+    dev = fixed.array.device
+    center = np.asarray(fixed.compute_center(), dtype=np.float64)
+    p2w = G.index_to_physical(fixed.grid, "itk")
+    w2p = G.physical_to_index(moving.grid, "itk")
+    is_ssd = cfg.metric == "ssd"
+    if cfg.metric not in ("ssd", "mi"):
+        raise ValueError("metric must be 'ssd' or 'mi'")
+    k0, k1 = slab_of(fixed.array.shape[0], rank, world)
+    slab = fixed.array[k0:k1] if k1 > k0 else None
+    ws = kernels.MetricWorkspace(dev, n_mats=N_PROBES, bins=cfg.bins)
+    d_A = torch.zeros((N_PROBES, 3, 4), dtype=torch.float64, device=dev)
+    d_Aloc = torch.zeros_like(d_A)
+    state = torch.zeros(int(lib.mia_optimizer_state_bytes()), dtype=torch.uint8, device=dev)
+    if not is_ssd:
+        if cfg.frange and cfg.mrange:
+            frange, mrange = cfg.frange, cfg.mrange
+        else:                                   # ranges must be global: reduce min / max over the slabs
+            lo_hi = torch.tensor([float("inf"), float("-inf")], dtype=torch.float64, device=dev)
+            if slab is not None:
+                lo_hi = torch.stack([slab.min().double(), slab.max().double()])
+            if world > 1:
+                neg = torch.stack([-lo_hi[0], lo_hi[1]])
+                dist.all_reduce(neg, op=dist.ReduceOp.MAX, group=group)
+                lo_hi = torch.stack([-neg[0], neg[1]])
+            frange = cfg.frange or (float(lo_hi[0]), float(lo_hi[1]))
+            mrange = cfg.mrange or _intensity_range(moving.array)
+
+    def stream():
+        return ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+    with torch.cuda.device(dev):
+        _lib.check(lib.mia_optimizer_init(state.data_ptr(), _lib.darr(params0), _lib.darr(center),
+                                          _lib.darr(p2w.ravel()), _lib.darr(w2p.ravel()), cfg.rot_step_deg,
+                                          cfg.trans_step_mm, cfg.min_step_scale, 0 if is_ssd else 1,
+                                          d_A.data_ptr(), stream()))
+        for _ in range(cfg.iterations):
+            if slab is not None:
+                d_Aloc.copy_(d_A)
+                d_Aloc[:, :, 3] += d_A[:, :, 2] * float(k0)
+            if is_ssd:
+                if slab is not None:
+                    kernels.resample_ssd(slab, moving.array, d_A=d_Aloc, mode=cfg.mode, ws=ws)
+                else:
+                    ws.ssd.zero_(); ws.count.zero_()
+                all_reduce_sum(ws.ssd, ws.count, group=group)
+                metric = ws.ssd
+            else:
+                if slab is not None:
+                    kernels.resample_jointhist(slab, moving.array, frange, mrange, bins=cfg.bins, d_A=d_Aloc,
+                                               mode=cfg.mode, ws=ws)
+                else:
+                    ws.hist.zero_(); ws.count.zero_()
+                all_reduce_sum(ws.hist, ws.count, group=group)
+                kernels.mi_from_hist(ws.hist, out=ws.mi)
+                metric = ws.mi
+            _lib.check(lib.mia_optimizer_step(state.data_ptr(), metric.data_ptr(), ws.count.data_ptr(),
+                                              1 if is_ssd else 0, d_A.data_ptr(), stream()))
+        n = min(cfg.iterations, 4096)
+        params = (ctypes.c_double * 6)()
+        scale = ctypes.c_double()
+        iters, conv, nrej = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        hc = np.zeros(n); hp = np.zeros((n, 6)); hs = np.zeros(n)
+        dp = ctypes.POINTER(ctypes.c_double)
+        _lib.check(lib.mia_optimizer_read(state.data_ptr(), params, ctypes.byref(scale), ctypes.byref(iters),
+                                          ctypes.byref(conv), ctypes.byref(nrej), hc.ctypes.data_as(dp),
+                                          hp.ctypes.data_as(dp), hs.ctypes.data_as(dp), n, stream()))
+    p = np.array(list(params))
+    return RegistrationResult(params=p, matrix=G.params_to_matrix(p, center), iterations=int(iters.value),
+                              converged=bool(conv.value), n_reject=int(nrej.value), cost_history=hc[:iters.value],
+                              param_history=hp[:iters.value], scale_history=hs[:iters.value],
+                              evaluations=N_PROBES * int(iters.value), extra={"slab": (k0, k1), "world": world})

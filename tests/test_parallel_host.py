@@ -1,0 +1,102 @@
+"""CPU tests of the z-slab sharding logic: slab arithmetic, and a world_size-2 gloo run in which
+each rank evaluates its slab with the ORACLE (there is no GPU here) and the all-reduced partials must equal
+the whole-volume oracle result -- histograms and counts bit for bit, SSD to 1e-12."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from medicalimageanalysis_b200 import geometry as G
+from medicalimageanalysis_b200 import parallel as P
+from medicalimageanalysis_b200.phantom import make_phantom
+from oracle import native
+
+
+def test_slab_bounds_cover_and_align():
+    for nz in (0, 1, 7, 8, 9, 100, 300, 317, 1200):
+        for world in (1, 2, 3, 4, 8):
+            b = P.slab_bounds(nz, world)
+            assert b[0] == 0 and b[-1] == nz and len(b) == world + 1
+            assert all(b[i] <= b[i + 1] for i in range(world))
+            assert all(x % P.TILE_Z == 0 for x in b[1:-1] if x != nz)
+            sizes = [b[i + 1] - b[i] for i in range(world)]
+            assert max(sizes) - min(s for s in sizes) <= 2 * P.TILE_Z or nz < world * P.TILE_Z
+
+
+def test_shift_matrix_is_the_slab_rule():
+    rng = np.random.default_rng(0)
+    A = rng.normal(size=(5, 3, 4))
+    S = P.shift_matrix(A, 7)
+    k = np.array([3.0, 4.0, 2.0, 1.0])
+    kk = np.array([3.0, 4.0, 9.0, 1.0])
+    assert np.allclose(S @ k, A @ kk) and not np.shares_memory(S, A)
+    St = P.shift_matrix(torch.from_numpy(A), 7)
+    assert np.allclose(St.numpy(), S)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        shape, sp = (20, 24, 40), (1.0, 1.0, 2.0)
+        g = G.Grid((shape[2], shape[1], shape[0]), sp, tuple(-0.5 * np.array(sp) * np.array(shape[::-1])))
+        fixed = make_phantom(shape, "CT", seed=3, spacing=sp)
+        moving = make_phantom(shape, "CT", seed=4, spacing=sp)
+        A = np.stack([G.compose_index_matrix(g, g, G.params_to_matrix(p, (0, 0, 0)))
+                      for p in ([2, -1, 3, 1, 2, -1], [0, 0, 0, 0.5, 0, 0])])
+        fr = (-1024.0, 3071.0)
+
+        def ev_ssd(k0, k1, As):
+            r = [native.reslice_ssd(fixed[k0:k1], moving, a, "itk") for a in As]
+            return torch.tensor([x[0] for x in r], dtype=torch.float64), torch.tensor([x[1] for x in r], dtype=torch.int64)
+
+        def ev_hist(k0, k1, As):
+            r = [native.joint_hist(fixed[k0:k1], moving, a, 16, fr, fr, "itk") for a in As]
+            return (torch.from_numpy(np.stack([x[0].astype(np.int64) for x in r])),
+                    torch.tensor([x[1] for x in r], dtype=torch.int64))
+
+        ssd, cnt = P.sharded_ssd(ev_ssd, shape[0], A, rank, world)
+        h, hc = P.sharded_hist(ev_hist, shape[0], A, 16, rank, world)
+        if rank == 0:
+            q.put((ssd.numpy(), cnt.numpy(), h.numpy(), hc.numpy()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_gloo_sharded_metrics_equal_the_whole(world):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    ssd, cnt, h, hc = got
+    shape, sp = (20, 24, 40), (1.0, 1.0, 2.0)
+    g = G.Grid((shape[2], shape[1], shape[0]), sp, tuple(-0.5 * np.array(sp) * np.array(shape[::-1])))
+    fixed = make_phantom(shape, "CT", seed=3, spacing=sp)
+    moving = make_phantom(shape, "CT", seed=4, spacing=sp)
+    fr = (-1024.0, 3071.0)
+    for i, p in enumerate(([2, -1, 3, 1, 2, -1], [0, 0, 0, 0.5, 0, 0])):
+        A = G.compose_index_matrix(g, g, G.params_to_matrix(p, (0, 0, 0)))
+        want, n = native.reslice_ssd(fixed, moving, A, "itk")
+        assert cnt[i] == n and abs(ssd[i] - want) <= 1e-12 * want
+        H, hn = native.joint_hist(fixed, moving, A, 16, fr, fr, "itk")
+        assert hc[i] == hn and np.array_equal(h[i], H.astype(np.int64))
