@@ -99,7 +99,14 @@ int mia_permute_axes(const void *d_in, int dtype, const int idims[3], void *d_ou
         dim3 block(bx, 256 / bx);
         long long g = (rows + block.y - 1) / block.y;
         if (g > (long long)sms * 32) g = (long long)sms * 32;
-        if (dtype == MIA_I16) permute_rows_kernel<int16_t><<<(unsigned)g, block, 0, s>>>(p);
+        const bool vec = dtype == MIA_I16 && p.odim[2] % 8 == 0 && (((uintptr_t)d_in | (uintptr_t)d_out) & 15u) == 0;
+        if (vec) {
+            const unsigned cpr = (unsigned)p.odim[2] / 8u;
+            const unsigned long long nchunks = (unsigned long long)rows * cpr;
+            unsigned long long gb = (nchunks + 255u) / 256u;
+            if (gb > (unsigned long long)sms * 16) gb = (unsigned long long)sms * 16;
+            permute_rows_vec_i16_kernel<<<(unsigned)gb, 256, 0, s>>>(p, cpr, nchunks);
+        } else if (dtype == MIA_I16) permute_rows_kernel<int16_t><<<(unsigned)g, block, 0, s>>>(p);
         else permute_rows_kernel<float><<<(unsigned)g, block, 0, s>>>(p);
     } else {
         const int pa = perm[0] == 2 ? 0 : 1;   // output axis fed by input x
@@ -107,7 +114,13 @@ int mia_permute_axes(const void *d_in, int dtype, const int idims[3], void *d_ou
         const long long tiles = (long long)((p.idim[2] + 31) / 32) * ((p.idim[perm[2]] + 31) / 32) * p.odim[pc];
         long long g = tiles < (long long)sms * 32 ? tiles : (long long)sms * 32;
         dim3 block(32, 8);
-        if (dtype == MIA_I16) permute_transpose_kernel<int16_t><<<(unsigned)g, block, 0, s>>>(p, pa, pc);
+        const bool vec = dtype == MIA_I16 && p.idim[2] % 2 == 0 && p.idim[perm[2]] % 2 == 0 &&
+                         (((uintptr_t)d_in | (uintptr_t)d_out) & 3u) == 0;
+        if (vec) {
+            const long long vt = (long long)((p.idim[2] + 63) / 64) * ((p.idim[perm[2]] + 63) / 64) * p.odim[pc];
+            const long long vg = vt < 0x7fffffffLL ? vt : 0x7fffffffLL;       // one tile per block
+            permute_transpose_vec_i16_kernel<<<(unsigned)vg, 256, 0, s>>>(p, pa, pc);
+        } else if (dtype == MIA_I16) permute_transpose_kernel<int16_t><<<(unsigned)g, block, 0, s>>>(p, pa, pc);
         else permute_transpose_kernel<float><<<(unsigned)g, block, 0, s>>>(p, pa, pc);
     }
     CUDA_TRY(cudaGetLastError());

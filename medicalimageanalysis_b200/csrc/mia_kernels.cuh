@@ -332,4 +332,99 @@ __global__ void __launch_bounds__(256) permute_transpose_kernel(const PermParams
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// int16 fast paths of the FFS permutation: 16-byte / 4-byte accesses instead of 2-byte ones.
+// HBM-bound copies (4 B per voxel); the scalar kernels above remain for odd sizes.
+
+__device__ __forceinline__ unsigned swap_halves(unsigned w) { return __byte_perm(w, 0u, 0x1032); }
+
+// Path A (x stays x): one thread per 8-voxel chunk.  Needs odim[2] % 8 == 0 and 16-byte aligned bases.
+__global__ void __launch_bounds__(256) permute_rows_vec_i16_kernel(const PermParams p, unsigned chunks_per_row, unsigned long long nchunks)
+{
+    const uint4 *in = static_cast<const uint4 *>(p.in);
+    uint4 *out = static_cast<uint4 *>(p.out);
+    for (unsigned long long c = (unsigned long long)blockIdx.x * 256u + threadIdx.x; c < nchunks;
+         c += (unsigned long long)gridDim.x * 256u) {
+        const unsigned r = (unsigned)(c / chunks_per_row), cx = (unsigned)(c % chunks_per_row);
+        const int o0 = (int)(r / (unsigned)p.odim[1]), o1 = (int)(r % (unsigned)p.odim[1]);
+        int idx[3];
+        idx[p.perm[0]] = p.flip[0] ? p.odim[0] - 1 - o0 : o0;
+        idx[p.perm[1]] = p.flip[1] ? p.odim[1] - 1 - o1 : o1;
+        const size_t srow = ((size_t)idx[0] * p.idim[1] + idx[1]) * chunks_per_row;
+        uint4 v;
+        if (p.flip[2]) {
+            const uint4 s = __ldg(in + srow + (chunks_per_row - 1 - cx));
+            v.x = swap_halves(s.w); v.y = swap_halves(s.z); v.z = swap_halves(s.y); v.w = swap_halves(s.x);
+        } else {
+            v = __ldg(in + srow + cx);
+        }
+        out[c] = v;
+    }
+}
+
+// Path B (input x becomes output axis pa): 64 x 64 tile, 2x2 register transposes so that both the global
+// loads (along input x) and the global stores (along input q = output x) are 4-byte, 128 B per warp.
+// Needs even idim[2] and even idim[q].
+__global__ void __launch_bounds__(256) permute_transpose_vec_i16_kernel(const PermParams p, int pa, int pc)
+{
+    __shared__ unsigned te[32][33], to[32][33];      // even / odd input x; [x / 2][q / 2]
+    const int q = p.perm[2], c_in = p.perm[pc];
+    const int nxin = p.idim[2], nq = p.idim[q];
+    const int tiles_x = (nxin + 63) / 64, tiles_q = (nq + 63) / 64;
+    const long long ntiles = (long long)tiles_x * tiles_q * p.odim[pc];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // element strides: input axes [z,y,x] and output axes [z,y,x]
+    const size_t istr[3] = {(size_t)p.idim[1] * p.idim[2], (size_t)p.idim[2], 1};
+    const size_t ostr[3] = {(size_t)p.odim[1] * p.odim[2], (size_t)p.odim[2], 1};
+    const unsigned sq = (unsigned)istr[q];             // input stride of the axis that becomes output x
+    const unsigned sa = (unsigned)ostr[pa];            // output stride of the axis fed by input x
+    for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const int tx0 = (int)(t % tiles_x) * 64;
+        const long long t2 = t / tiles_x;
+        const int tq0 = (int)(t2 % tiles_q) * 64;
+        const int oc = (int)(t2 / tiles_q);
+        const int ic = p.flip[pc] ? p.odim[pc] - 1 - oc : oc;
+        // tile bases (64-bit once per tile); everything inside the tile is a 32-bit offset
+        const int16_t *ibase = static_cast<const int16_t *>(p.in) + (size_t)ic * istr[c_in] + (size_t)tq0 * sq + tx0;
+        const int xo0 = p.flip[pa] ? nxin - 1 - tx0 : tx0;          // output index along pa of tile row 0
+        const int qo0 = p.flip[2] ? nq - 2 - tq0 : tq0;             // output x of the tile's first pair
+        int16_t *obase = static_cast<int16_t *>(p.out) + (size_t)oc * ostr[pc] + (size_t)xo0 * sa + qo0;
+        const int nxt = min(64, nxin - tx0), nqt = min(64, nq - tq0);
+        unsigned w0[4], w1[4];
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            const int rr = warp + 8 * it;
+            w0[it] = w1[it] = 0u;
+            if (2 * lane < nxt && 2 * rr < nqt) {
+                const unsigned e = (unsigned)(2 * rr) * sq + 2u * lane;
+                w0[it] = __ldg(reinterpret_cast<const unsigned *>(ibase + e));
+                w1[it] = __ldg(reinterpret_cast<const unsigned *>(ibase + e + sq));
+            }
+        }
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            const int rr = warp + 8 * it;
+            te[lane][rr] = __byte_perm(w0[it], w1[it], 0x5410);      // (a[q][x],   a[q+1][x])
+            to[lane][rr] = __byte_perm(w0[it], w1[it], 0x7632);      // (a[q][x+1], a[q+1][x+1])
+        }
+        __syncthreads();
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int xr = warp + 8 * it;
+            if (xr < nxt && 2 * lane < nqt) {
+                unsigned w = (xr & 1) ? to[xr >> 1][lane] : te[xr >> 1][lane];
+                const long long row = p.flip[pa] ? -(long long)xr * sa : (long long)xr * sa;
+                long long col = 2 * lane;
+                if (p.flip[2]) {
+                    col = -col;
+                    w = swap_halves(w);
+                }
+                *reinterpret_cast<unsigned *>(obase + row + col) = w;
+            }
+        }
+        __syncthreads();
+    }
+}
+
 }  // namespace mia

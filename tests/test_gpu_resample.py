@@ -88,6 +88,17 @@ def test_ffs_permutation_bit_exact(cuda_device, case, dtype):
     assert np.array_equal(got.cpu().numpy(), ffs.oracle_ffs(a, case))
 
 
+@pytest.mark.parametrize("case", list(kernels.FFS_PERMUTATIONS))
+@pytest.mark.parametrize("shape", [(36, 44, 72), (6, 10, 64), (130, 66, 200), (2, 2, 8)])
+def test_ffs_permutation_vector_paths_bit_exact(cuda_device, case, shape):
+    """Even sizes take the 16-byte row copy / 64x64 2x2-register transpose kernels (int16 only)."""
+    rng = np.random.default_rng(5)
+    a = rng.integers(-32768, 32767, size=shape).astype(np.int16)
+    perm, flip = kernels.FFS_PERMUTATIONS[case]
+    got = kernels.permute_axes(torch.from_numpy(a).to(cuda_device), perm, flip)
+    assert np.array_equal(got.cpu().numpy(), ffs.oracle_ffs(a, case))
+
+
 @pytest.mark.parametrize("case", ["axial_k1", "axial_k2", "axial_k3"])
 def test_ffs_as_a_signed_permutation_matrix_through_the_resampler(cuda_device, golden, case):
     """the FFS permutation is a 4x4 signed permutation whose trilinear weights are 0/1, so the
