@@ -170,10 +170,9 @@ bool tile_path_disabled()
 }
 
 // Builds the 3-D tensor map of the moving volume with the box of BoxFor<TM>.  False => not eligible.
-template <typename TM>
+template <typename TM, class BOX>
 bool make_tensor_map(CUtensorMap *map, const void *d_mov, const int mdims[3])
 {
-    using BOX = typename BoxFor<TM>::type;
     if (tile_path_disabled()) return false;
     EncodeTiledFn enc = encode_tiled_fn();
     if (!enc) return false;
@@ -191,10 +190,9 @@ bool make_tensor_map(CUtensorMap *map, const void *d_mov, const int mdims[3])
 }
 
 // Does a typical tile of this host matrix fit the box?  (Device matrices are classified per tile.)
-template <typename TM>
+template <typename TM, class BOX>
 bool box_fits(const double *A)
 {
-    using BOX = typename BoxFor<TM>::type;
     const Reach r = tile_reach(A);
     const int B[3] = {BOX::kX, BOX::kY, BOX::kZ};
     for (int a = 0; a < 3; ++a)
@@ -209,10 +207,9 @@ void fill_tile(KParams &p)
     p.ntiles = (long long)p.ntx * p.nty * ((p.oz + kTZ - 1) / kTZ);
 }
 
-template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK>
+template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, class BOX>
 int launch_tile(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream_t s)
 {
-    using BOX = typename BoxFor<TM>::type;
     constexpr int MINB = sizeof(TM) == 2 ? 3 : 2;
     constexpr int NST = StagesFor<TM>::value;
     auto k = tile_kernel<TM, TF, TO, METRIC, STORE, VTK, BOX, NST, MINB>;
@@ -245,6 +242,24 @@ int launch_tile(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream
 }
 
 
+// One (element type, box) attempt: fit test for host matrices, tensor map, launch.
+template <int METRIC, bool STORE, typename TM, class BOX>
+int try_tile_box(int mode, const void *d_mov, const int mdims[3], const double *A_host, int n_mats, KParams p,
+                 cudaStream_t s, bool &launched)
+{
+    launched = false;
+    alignas(64) CUtensorMap map;
+    for (int m = 0; A_host && m < n_mats; ++m)
+        if (!box_fits<TM, BOX>(A_host + 12 * m)) return MIA_OK;
+    if (!make_tensor_map<TM, BOX>(&map, d_mov, mdims)) return MIA_OK;
+    fill_tile(p);
+    if (p.ntiles > 0x7fffffffLL) return MIA_OK;
+    if ((long long)p.ox * p.oy * kTZ >= 0x7fffffffLL) return MIA_OK;   // in-tile plane offsets are 32-bit
+    launched = true;
+    return mode == MIA_MODE_VTK ? launch_tile<TM, TM, TM, METRIC, STORE, true, BOX>(map, p, n_mats, s)
+                                : launch_tile<TM, TM, TM, METRIC, STORE, false, BOX>(map, p, n_mats, s);
+}
+
 // Try the tile path for (dtype, mode); `launched` tells whether it took the call.  A_host may be null
 // (device matrices: the kernel classifies every tile itself and falls back per tile).
 template <int METRIC, bool STORE>
@@ -252,26 +267,9 @@ int try_tile(int dtype, int mode, const void *d_mov, const int mdims[3], const d
              KParams p, cudaStream_t s, bool &launched)
 {
     launched = false;
-    alignas(64) CUtensorMap map;
-    const bool vtk = mode == MIA_MODE_VTK;
-    if (dtype == MIA_I16) {
-        for (int m = 0; A_host && m < n_mats; ++m)
-            if (!box_fits<int16_t>(A_host + 12 * m)) return MIA_OK;
-        if (!make_tensor_map<int16_t>(&map, d_mov, mdims)) return MIA_OK;
-    } else {
-        for (int m = 0; A_host && m < n_mats; ++m)
-            if (!box_fits<float>(A_host + 12 * m)) return MIA_OK;
-        if (!make_tensor_map<float>(&map, d_mov, mdims)) return MIA_OK;
-    }
-    fill_tile(p);
-    if (p.ntiles > 0x7fffffffLL) return MIA_OK;
-    if ((long long)p.ox * p.oy * kTZ >= 0x7fffffffLL) return MIA_OK;   // in-tile plane offsets are 32-bit
-    launched = true;
-    if (dtype == MIA_I16)
-        return vtk ? launch_tile<int16_t, int16_t, int16_t, METRIC, STORE, true>(map, p, n_mats, s)
-                   : launch_tile<int16_t, int16_t, int16_t, METRIC, STORE, false>(map, p, n_mats, s);
-    return vtk ? launch_tile<float, float, float, METRIC, STORE, true>(map, p, n_mats, s)
-               : launch_tile<float, float, float, METRIC, STORE, false>(map, p, n_mats, s);
+    if (dtype == MIA_F32)
+        return try_tile_box<METRIC, STORE, float, BoxFor<float>::type>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
+    return try_tile_box<METRIC, STORE, int16_t, BoxFor<int16_t>::type>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
 }
 
 }  // namespace
