@@ -140,7 +140,18 @@ template <typename TM> struct BoxFor;
 #define MIA_NST_I16 2
 #endif
 template <> struct BoxFor<int16_t> { using type = Box<MIA_BX_I16, MIA_BY_I16, MIA_BZ_I16>; };   // 64 shorts = 32 words: row pitch = 0 mod 32 banks
-template <> struct BoxFor<float>   { using type = Box<40, 18, 14>; };
+#ifndef MIA_BX_F32
+#define MIA_BX_F32 64     // 64 words: row and plane pitch = 0 mod 32 banks, so a warp whose 32 x-neighbours cross
+#define MIA_BY_F32 15     // rows / planes of the box still hits 32 different banks (pitch 40 cost 2.4 wavefronts
+#define MIA_BZ_F32 14     // per LDS at config-3 angles, ncu r01 prof_c3); 2 stages x 2 CTAs fill the 228 KB
+#endif
+template <> struct BoxFor<float>   { using type = Box<MIA_BX_F32, MIA_BY_F32, MIA_BZ_F32>; };
+#ifndef MIA_BX_F32H       // joint-histogram kernels carry bins^2 counters per CTA next to the ring
+#define MIA_BX_F32H 64
+#define MIA_BY_F32H 14
+#define MIA_BZ_F32H 13
+#endif
+using BoxF32Hist = Box<MIA_BX_F32H, MIA_BY_F32H, MIA_BZ_F32H>;
 template <typename TM> struct StagesFor { static constexpr int value = sizeof(TM) == 2 ? MIA_NST_I16 : 2; };
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
@@ -253,6 +264,7 @@ int try_tile_box(int mode, const void *d_mov, const int mdims[3], const double *
         if (!box_fits<TM, BOX>(A_host + 12 * m)) return MIA_OK;
     if (!make_tensor_map<TM, BOX>(&map, d_mov, mdims)) return MIA_OK;
     fill_tile(p);
+    p.magic_fold = 0u - kMagicBits * (unsigned)((BOX::kY + 1) * BOX::kX + 1) * (unsigned)sizeof(TM);
     if (p.ntiles > 0x7fffffffLL) return MIA_OK;
     if ((long long)p.ox * p.oy * kTZ >= 0x7fffffffLL) return MIA_OK;   // in-tile plane offsets are 32-bit
     launched = true;
@@ -267,8 +279,11 @@ int try_tile(int dtype, int mode, const void *d_mov, const int mdims[3], const d
              KParams p, cudaStream_t s, bool &launched)
 {
     launched = false;
-    if (dtype == MIA_F32)
+    if (dtype == MIA_F32) {
+        if (METRIC == kHist)
+            return try_tile_box<METRIC, STORE, float, BoxF32Hist>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
         return try_tile_box<METRIC, STORE, float, BoxFor<float>::type>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
+    }
     return try_tile_box<METRIC, STORE, int16_t, BoxFor<int16_t>::type>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
 }
 

@@ -12,6 +12,7 @@ struct KParams {
     void *out;                   // resampled output or nullptr
     int ox, oy, oz;              // output lattice
     int ntx, nty;                // tiles along x / y
+    unsigned magic_fold;         // tile path: -(kMagicBits * ((BY+1)*BX+1)) * sizeof(TM) mod 2^32, see tile_compute
     long long ntiles;            // ntx * nty * oz
     Mat34 A0;                    // matrix 0 by value (host-matrix path, n_mats == 1)
     const double *dA;            // [n_mats][12] device matrices, or nullptr -> A0

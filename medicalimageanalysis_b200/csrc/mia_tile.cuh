@@ -303,9 +303,9 @@ __device__ __forceinline__ void tile_compute(const KParams &p, const unsigned ch
     const float fz = (float)((unsigned)tz64 >> 8) * 5.9604644775390625e-8f;
     // element index = ((iz*BY + iy)*BX + ix) with i* = thread base + floor(local); floor(local) arrives as the
     // raw bits of (local + kMagic), i.e. kMagicBits + floor: the constant part is folded into ubase (mod 2^32)
-    const uint32_t ubase = smem_u32(stage) +
-                           ((uint32_t)((tbz * BOX::kY + tby) * BOX::kX + tbx) -
-                            kMagicBits * (uint32_t)((BOX::kY + 1) * BOX::kX + 1)) * ES;
+    // (p.magic_fold is a launch parameter on purpose: as a literal, ptxas pulls it back out of ubase and
+    // re-adds it in front of every LDS -- 8 extra VIADD per voxel in the float32 kernels)
+    const uint32_t ubase = smem_u32(stage) + (uint32_t)((tbz * BOX::kY + tby) * BOX::kX + tbx) * ES + p.magic_fold;
 
     float ilox = 0.f, ihix = 0.f, iloy = 0.f, ihiy = 0.f, iloz = 0.f, ihiz = 0.f;
     float clox = 0.f, chix = 0.f, cloy = 0.f, chiy = 0.f, cloz = 0.f, chiz = 0.f;
@@ -327,9 +327,15 @@ __device__ __forceinline__ void tile_compute(const KParams &p, const unsigned ch
 
     float fv[kTZ];
     if (METRIC != kNone) {
+        // one 64-bit pointer stepped by a 32-bit plane pitch (2 instructions per load); left to itself the
+        // compiler rebuilds base + index * 4 from the constant bank for every plane (5 per load)
+        const TF *fp = fixed;
 #pragma unroll
-        for (int kz = 0; kz < kTZ; ++kz)
-            fv[kz] = (row_ok && kz < kcnt) ? (float)__ldg(fixed + (unsigned)kz * plane) : 0.0f;
+        for (int kz = 0; kz < kTZ; ++kz) {
+            asm("" : "+l"(fp));
+            fv[kz] = (row_ok && kz < kcnt) ? (float)__ldg(fp) : 0.0f;
+            fp += plane;
+        }
     }
 
     const f32x2 ax2 = pk(g.a2x, g.a2x), ay2 = pk(g.a2y, g.a2y), az2 = pk(g.a2z, g.a2z);
