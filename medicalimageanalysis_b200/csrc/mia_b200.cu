@@ -152,6 +152,12 @@ template <> struct BoxFor<float>   { using type = Box<MIA_BX_F32, MIA_BY_F32, MI
 #define MIA_BZ_F32H 13
 #endif
 using BoxF32Hist = Box<MIA_BX_F32H, MIA_BY_F32H, MIA_BZ_F32H>;
+#ifndef MIA_BX_I16H
+#define MIA_BX_I16H 64
+#define MIA_BY_I16H 16
+#define MIA_BZ_I16H 12
+#endif
+using BoxI16Hist = Box<MIA_BX_I16H, MIA_BY_I16H, MIA_BZ_I16H>;
 template <typename TM> struct StagesFor { static constexpr int value = sizeof(TM) == 2 ? MIA_NST_I16 : 2; };
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
@@ -221,9 +227,16 @@ void fill_tile(KParams &p)
 template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, class BOX>
 int launch_tile(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream_t s)
 {
-    constexpr int MINB = sizeof(TM) == 2 ? 3 : 2;
+#ifndef MIA_MINB_I16M
+#define MIA_MINB_I16M 3
+#endif
+    constexpr int MINB = sizeof(TM) == 2 ? (METRIC == kNone ? 3 : MIA_MINB_I16M) : 2;
     constexpr int NST = StagesFor<TM>::value;
-    auto k = tile_kernel<TM, TF, TO, METRIC, STORE, VTK, BOX, NST, MINB>;
+#ifndef MIA_PREFETCH_RULE
+#define MIA_PREFETCH_RULE (sizeof(TM) == 4 && METRIC == kHist)
+#endif
+    constexpr bool PREFETCH = MIA_PREFETCH_RULE;      // measured per kernel family, see tile_compute
+    auto k = tile_kernel<TM, TF, TO, METRIC, STORE, VTK, BOX, NST, MINB, PREFETCH>;
     const size_t smem = TileSmem<TM, BOX, NST>::bytes(METRIC == kHist ? p.bins : 0);
     static std::mutex mu;
     static std::map<std::pair<int, size_t>, int> occ;     // (device, smem) -> resident CTAs per SM
@@ -280,11 +293,15 @@ int try_tile(int dtype, int mode, const void *d_mov, const int mdims[3], const d
 {
     launched = false;
     if (dtype == MIA_F32) {
-        if (METRIC == kHist)
+        if constexpr (METRIC == kHist)
             return try_tile_box<METRIC, STORE, float, BoxF32Hist>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
-        return try_tile_box<METRIC, STORE, float, BoxFor<float>::type>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
+        else
+            return try_tile_box<METRIC, STORE, float, BoxFor<float>::type>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
     }
-    return try_tile_box<METRIC, STORE, int16_t, BoxFor<int16_t>::type>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
+    if constexpr (METRIC == kHist)
+        return try_tile_box<METRIC, STORE, int16_t, BoxI16Hist>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
+    else
+        return try_tile_box<METRIC, STORE, int16_t, BoxFor<int16_t>::type>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
 }
 
 }  // namespace

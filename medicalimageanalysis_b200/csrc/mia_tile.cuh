@@ -261,7 +261,30 @@ __device__ __forceinline__ f32x2 add2_rm(f32x2 a, f32x2 b)
     asm("add.rm.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
     return r;
 }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b)
+{
+    f32x2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
 __device__ __forceinline__ f32x2 lerp2(f32x2 w, f32x2 a, f32x2 b) { return fma2(w, sub2(b, a), a); }
+
+// Histogram bins of a voxel pair as raw bits kMagicBits + bin: the arithmetic of bin_of() -- (v - vmin) * scale
+// with separate roundings, clamp, floor -- with the floor taken by a round-down add of 1.5 * 2^23 instead of
+// FRND + F2I (both quarter-rate XU) and the pair sharing the packed instructions.  Clamping to the integers
+// [0, bins-1] before the floor equals clamping after it; NaN goes to bin 0 through fmaxf as in bin_of().
+__device__ __forceinline__ f32x2 bin_bits2(f32x2 v2, f32x2 vmin2, f32x2 scale2, float binmax, f32x2 magic2)
+{
+    float b0, b1;
+    upk(mul2(sub2(v2, vmin2), scale2), b0, b1);
+    b0 = fminf(fmaxf(b0, 0.0f), binmax);
+    b1 = fminf(fmaxf(b1, 0.0f), binmax);
+    return add2_rm(pk(b0, b1), magic2);
+}
+__device__ __forceinline__ void red_shared_inc(uint32_t addr)
+{
+    asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(addr) : "memory");
+}
 
 // Per-thread constants of a launch: (lane * A[:,0] + warp * A[:,1]) in Q31.32 and the z column in float32.
 struct ThreadGeom {
@@ -279,14 +302,28 @@ __device__ __forceinline__ ThreadGeom make_thread_geom(const double *A, int lane
     return g;
 }
 
+// Fixed-image values of one tile for this thread (all 8 planes at once): the prologue of the consumer loop and
+// the tiles that bypass tile_compute.
+template <typename TF>
+__device__ __forceinline__ void load_fixed(float (&fv)[kTZ], const TF *fp, int nk, unsigned plane)
+{
+#pragma unroll
+    for (int kz = 0; kz < kTZ; ++kz) {
+        asm("" : "+l"(fp));
+        fv[kz] = kz < nk ? (float)__ldg(fp) : 0.0f;
+        fp += plane;
+    }
+}
+
 // One consumer thread's share of one tile whose box is resident in shared memory: the 8 z planes of
 // output voxel column (i0 + lane, j0 + warp), as 4 packed pairs.  BORDER adds the inside test and the
 // coordinate clamp (== VTK/ITK index clamp: the clamped coordinate has weight 0 on the tap beyond the edge,
 // which TMA zero-filled); interior tiles need neither.
-template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, bool BORDER, class BOX>
+template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, bool BORDER, class BOX, bool PREFETCH>
 __device__ __forceinline__ void tile_compute(const KParams &p, const unsigned char *stage, const TileInfo &ti,
                                              const ThreadGeom &g, int i0, int j0, int k0, int lane, int warp,
-                                             double &acc, unsigned &cnt, unsigned *s_hist)
+                                             double &acc, unsigned &cnt, unsigned *s_hist, float (&fv)[kTZ],
+                                             const TF *nfp, int nk)
 {
     static_assert(kTZ % 2 == 0, "voxels are processed in z pairs");
     constexpr unsigned ES = sizeof(TM);
@@ -321,27 +358,24 @@ __device__ __forceinline__ void tile_compute(const KParams &p, const unsigned ch
     // the host guarantees 8 * oy * ox < 2^31, so plane offsets inside a tile are 32-bit
     const unsigned plane = (unsigned)p.oy * (unsigned)p.ox;
     const size_t gofs = ((size_t)k0 * p.oy + j) * p.ox + i;
-    const TF *fixed = static_cast<const TF *>(p.fixed) + gofs;
     TO *out = static_cast<TO *>(p.out) + gofs;
     const TO bgv = tile_to_out<TO, VTK>(p.background);
 
-    float fv[kTZ];
-    if (METRIC != kNone) {
-        // one 64-bit pointer stepped by a 32-bit plane pitch (2 instructions per load); left to itself the
-        // compiler rebuilds base + index * 4 from the constant bank for every plane (5 per load)
-        const TF *fp = fixed;
-#pragma unroll
-        for (int kz = 0; kz < kTZ; ++kz) {
-            asm("" : "+l"(fp));
-            fv[kz] = (row_ok && kz < kcnt) ? (float)__ldg(fp) : 0.0f;
-            fp += plane;
-        }
-    }
-
+    // fv[] holds this thread's 8 fixed-image values of THIS tile.  PREFETCH: they were fetched while the previous
+    // tile was computed, and each pair reloads its two registers with the next tile's values (nfp / nk) as soon
+    // as it has used them, so the global-load latency hides behind a whole tile of arithmetic.  Otherwise they
+    // are loaded here (nfp / nk then describe this tile): the 72-register int16 kernels spill with the longer
+    // live ranges, and lose more than the latency costs them.
+    if (METRIC != kNone && !PREFETCH) load_fixed<TF>(fv, nfp, nk, plane);
     const f32x2 ax2 = pk(g.a2x, g.a2x), ay2 = pk(g.a2y, g.a2y), az2 = pk(g.a2z, g.a2z);
     const f32x2 fx2 = pk(fx, fx), fy2 = pk(fy, fy), fz2 = pk(fz, fz);
     const f32x2 magic2 = pk(kMagic, kMagic);
     f32x2 part2 = pk(0.0f, 0.0f);
+    const uint32_t hrow = 4u * (uint32_t)p.bins;
+    const uint32_t hconst = smem_u32(s_hist) - 4u * kMagicBits - hrow * kMagicBits;
+    const float binmax = (float)(p.bins - 1);
+    const f32x2 fmin2 = pk(p.fmin, p.fmin), fsc2 = pk(p.fscale, p.fscale);
+    const f32x2 mmin2 = pk(p.mmin, p.mmin), msc2 = pk(p.mscale, p.mscale);
 #pragma unroll
     for (int kp = 0; kp < kTZ; kp += 2) {
         const f32x2 kk = pk((float)kp, (float)(kp + 1));
@@ -393,14 +427,22 @@ __device__ __forceinline__ void tile_compute(const KParams &p, const unsigned ch
             cnt += (u0 ? 1u : 0u) + (u1 ? 1u : 0u);
         }
         if (METRIC == kHist) {
-            if (live0 && in0) {
-                atomicAdd(&s_hist[bin_of(fv[kp], p.fmin, p.fscale, p.bins) * p.bins + bin_of(val0, p.mmin, p.mscale, p.bins)], 1u);
-                ++cnt;
-            }
-            if (live1 && in1) {
-                atomicAdd(&s_hist[bin_of(fv[kp + 1], p.fmin, p.fscale, p.bins) * p.bins + bin_of(val1, p.mmin, p.mscale, p.bins)], 1u);
-                ++cnt;
-            }
+            // counter address = hist + 4 * (fbin * bins + mbin); the magic bits of both bin words are folded into
+            // hconst.  The voxel count is not kept here: it is the sum of the histogram (kernel epilogue).
+            const f32x2 fb2 = bin_bits2(pk(fv[kp], fv[kp + 1]), fmin2, fsc2, binmax, magic2);
+            const f32x2 mb2 = bin_bits2(val2, mmin2, msc2, binmax, magic2);
+            const uint32_t h0 = mad_u32((uint32_t)mb2, 4u, mad_u32((uint32_t)fb2, hrow, hconst));
+            const uint32_t h1 = mad_u32((uint32_t)(mb2 >> 32), 4u, mad_u32((uint32_t)(fb2 >> 32), hrow, hconst));
+            if (live0 && in0) red_shared_inc(h0);
+            if (live1 && in1) red_shared_inc(h1);
+        }
+        if (METRIC != kNone && PREFETCH) {
+            asm("" : "+l"(nfp));                     // keep ONE stepped 64-bit pointer (2 instructions per load)
+            fv[kp] = kp < nk ? (float)__ldg(nfp) : 0.0f;
+            nfp += plane;
+            asm("" : "+l"(nfp));
+            fv[kp + 1] = kp + 1 < nk ? (float)__ldg(nfp) : 0.0f;
+            nfp += plane;
         }
     }
     if (METRIC == kSsd) {
@@ -461,7 +503,7 @@ struct TileSmem {
     static size_t bytes(int bins) { return (size_t)kHistOff + sizeof(unsigned) * (size_t)bins * bins; }
 };
 
-template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, class BOX, int NST, int MINB>
+template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, class BOX, int NST, int MINB, bool PREFETCH>
 __global__ void __launch_bounds__(kTileThreads, MINB)
 tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ KParams p)
 {
@@ -556,22 +598,44 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ KP
     } else {
         // ---------------- consumers: 8 warps ----------------
         const ThreadGeom geom = make_thread_geom(A, lane, warp);
+        const unsigned plane = (unsigned)p.oy * (unsigned)p.ox;
+        // this thread's column of the fixed image in tile (a, b, c): pointer to its first plane, planes to read
+        auto fixed_col = [&](int a, int b, int c, int &nk) -> const TF * {
+            const int i = a * kTX + lane, j = b * kTY + warp, k0 = c * kTZ;
+            nk = (i < p.ox && j < p.oy) ? min(kTZ, p.oz - k0) : 0;
+            return static_cast<const TF *>(p.fixed) + (((size_t)k0 * p.oy + j) * p.ox + i);
+        };
+        float fv[kTZ];
+        if (METRIC != kNone && PREFETCH) {
+            int nk0 = 0;
+            const TF *fp0 = ntile_mine > 0 ? fixed_col(tix, tiy, tiz, nk0) : nullptr;
+            load_fixed<TF>(fv, fp0, nk0, plane);
+        }
         unsigned s = 0, ph = 0;
         for (int n = 0; n < ntile_mine; ++n) {
             const int i0 = tix * kTX, j0 = tiy * kTY, k0 = tiz * kTZ;
+            int nk = 0;
+            const TF *nfp = nullptr;
+            if (METRIC != kNone && !PREFETCH) nfp = fixed_col(tix, tiy, tiz, nk);
+            advance();                                   // (tix, tiy, tiz) is now the NEXT tile
+            if (METRIC != kNone && PREFETCH && n + 1 < ntile_mine) nfp = fixed_col(tix, tiy, tiz, nk);
             mbar_wait<32>(bar0 + 8 * s, ph);
             const TileInfo ti = infos[n & 63];
             const unsigned char *stage = tsm + L::kStageBytes * s;
-            if (ti.cls == kInterior)
-                tile_compute<TM, TF, TO, METRIC, STORE, VTK, false, BOX>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt, s_hist);
-            else if (ti.cls == kBorder)
-                tile_compute<TM, TF, TO, METRIC, STORE, VTK, true, BOX>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt, s_hist);
-            else if (STORE || ti.cls == kNoFit)
-                tile_compute_nobox<TM, TF, TO, METRIC, STORE, VTK>(p, p.dA ? p.dA + 12 * m : p.A0.a, ti.cls, i0, j0, k0, lane, warp,
-                                                                   acc, cnt, s_hist);
+            if (ti.cls == kInterior) {
+                tile_compute<TM, TF, TO, METRIC, STORE, VTK, false, BOX, PREFETCH>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt, s_hist,
+                                                                         fv, nfp, nk);
+            } else if (ti.cls == kBorder) {
+                tile_compute<TM, TF, TO, METRIC, STORE, VTK, true, BOX, PREFETCH>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt, s_hist,
+                                                                        fv, nfp, nk);
+            } else {
+                if (STORE || ti.cls == kNoFit)
+                    tile_compute_nobox<TM, TF, TO, METRIC, STORE, VTK>(p, p.dA ? p.dA + 12 * m : p.A0.a, ti.cls, i0, j0, k0, lane, warp,
+                                                                       acc, cnt, s_hist);
+                if (METRIC != kNone && PREFETCH) load_fixed<TF>(fv, nfp, nk, plane);
+            }
             __syncwarp();
             if (lane == 0) mbar_arrive(bar0 + 8 * (NST + s));
-            advance();
             if (++s == NST) { s = 0; ph ^= 1u; }
         }
     }
@@ -583,19 +647,23 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ KP
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     }
+    if (METRIC == kHist) {
+        // flush the CTA's histogram; the number of voxels it counted is the sum of its bins
+        __syncthreads();
+        unsigned *gh = p.d_hist + (size_t)m * p.bins * p.bins;
+        cnt = 0;
+        for (int b = tid; b < p.bins * p.bins; b += kTileThreads) {
+            const unsigned c = s_hist[b];
+            if (c) atomicAdd(gh + b, c);
+            cnt += c;
+        }
+    }
     cnt = warp_sum_u(cnt);
     if (lane == 0) {
         s_red[warp] = acc;
         s_redc[warp] = cnt;
     }
     __syncthreads();
-    if (METRIC == kHist) {
-        unsigned *gh = p.d_hist + (size_t)m * p.bins * p.bins;
-        for (int b = tid; b < p.bins * p.bins; b += kTileThreads) {
-            const unsigned c = s_hist[b];
-            if (c) atomicAdd(gh + b, c);
-        }
-    }
     if (tid == 0) {
         double sacc = 0.0;
         unsigned long long c = 0;
