@@ -131,15 +131,21 @@ void dispatch_metric(int mov_dtype, int fixed_dtype, const KParams &p, int mode,
 thread_local int g_last_path = 0;    // 0 = direct kernel, 1 = tile kernel (diagnostic, mia_debug_last_path)
 
 template <typename TM> struct BoxFor;
-#ifndef MIA_BX_I16        // tuning builds override these with -D (see scripts/tune_variants.sh)
-#define MIA_BX_I16 64
-#define MIA_BY_I16 16
+// Box shapes (tuning builds override them with -D).  int16: 96 shorts = 48 words, and BY odd, make the row AND
+// the plane pitch = 16 mod 32 banks.  A warp's 32 x-neighbours cover at most 17 words, so the run that continues
+// on the next row / plane lands in the other half of the banks whatever the sign of the rotation: 1.26 wavefronts
+// per LDS in simulation at +-5 degrees against 1.75 for a 64-short pitch (where the two lanes that straddle the
+// row change share a bank half of the time).  The joint-histogram kernels keep the 64-wide box: with bins^2
+// counters beside the ring, the wide one would cost the third resident CTA.
+#ifndef MIA_BX_I16
+#define MIA_BX_I16 96
+#define MIA_BY_I16 15
 #define MIA_BZ_I16 12
 #endif
 #ifndef MIA_NST_I16
 #define MIA_NST_I16 2
 #endif
-template <> struct BoxFor<int16_t> { using type = Box<MIA_BX_I16, MIA_BY_I16, MIA_BZ_I16>; };   // 64 shorts = 32 words: row pitch = 0 mod 32 banks
+template <> struct BoxFor<int16_t> { using type = Box<MIA_BX_I16, MIA_BY_I16, MIA_BZ_I16>; };
 #ifndef MIA_BX_F32
 #define MIA_BX_F32 64     // 64 words: row and plane pitch = 0 mod 32 banks, so a warp whose 32 x-neighbours cross
 #define MIA_BY_F32 15     // rows / planes of the box still hits 32 different banks (pitch 40 cost 2.4 wavefronts

@@ -413,9 +413,14 @@ __device__ __forceinline__ void tile_compute(const KParams &p, const unsigned ch
         upk(val2, val0, val1);
         const bool live0 = row_ok && kp < kcnt, live1 = row_ok && kp + 1 < kcnt;
         if (STORE) {
+            // one 64-bit output pointer stepped by the plane pitch: 2 address instructions per store, not 5
             const TO o0 = tile_to_out<TO, VTK>(val0), o1 = tile_to_out<TO, VTK>(val1);
-            if (live0) st_out(out + (unsigned)kp * plane, in0 ? o0 : bgv);
-            if (live1) st_out(out + (unsigned)(kp + 1) * plane, in1 ? o1 : bgv);
+            asm("" : "+l"(out));
+            if (live0) st_out(out, in0 ? o0 : bgv);
+            out += plane;
+            asm("" : "+l"(out));
+            if (live1) st_out(out, in1 ? o1 : bgv);
+            out += plane;
         }
         if (METRIC == kSsd) {
             f32x2 d2 = sub2(pk(fv[kp], fv[kp + 1]), val2);
@@ -577,6 +582,9 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ KP
             infos[(base & 32) + lane] = mine;
             __syncwarp();
             const int cnt_pass = min(32, ntile_mine - base);
+            // (An L2 prefetch of the boxes 1 / 2 / 4 tiles ahead of the ring -- cp.async.bulk.prefetch.tensor -- was
+            // measured and made every kernel 2-17 % slower: the ring is short of L2->SM throughput, not of DRAM
+            // latency, and the prefetch adds L2 lookups.)
             for (int q = 0; q < cnt_pass; ++q) {
                 const int cls = __shfl_sync(0xffffffffu, mine.cls, q);
                 const int bx = __shfl_sync(0xffffffffu, mine.bx, q);
