@@ -130,41 +130,48 @@ void dispatch_metric(int mov_dtype, int fixed_dtype, const KParams &p, int mode,
 // 16-byte aligned base and row pitch.  Anything else goes to the direct kernel.
 thread_local int g_last_path = 0;    // 0 = direct kernel, 1 = tile kernel (diagnostic, mia_debug_last_path)
 
-template <typename TM> struct BoxFor;
-// Box shapes (tuning builds override them with -D).  int16: 96 shorts = 48 words, and BY odd, make the row AND
-// the plane pitch = 16 mod 32 banks.  A warp's 32 x-neighbours cover at most 17 words, so the run that continues
-// on the next row / plane lands in the other half of the banks whatever the sign of the rotation: 1.26 wavefronts
-// per LDS in simulation at +-5 degrees against 1.75 for a 64-short pitch (where the two lanes that straddle the
-// row change share a bank half of the time).  The joint-histogram kernels keep the 64-wide box: with bins^2
-// counters beside the ring, the wide one would cost the third resident CTA.
-#ifndef MIA_BX_I16
-#define MIA_BX_I16 96
-#define MIA_BY_I16 15
-#define MIA_BZ_I16 12
+// Per kernel family (element type x fused reduction): box shape, ring depth, resident CTAs per SM and whether
+// the fixed image is prefetched one tile ahead.  Every entry is a measured choice (profiles/);
+// tuning builds override them with -D.
+//
+// Bank rules behind the box shapes.  float32: 64 words make the row and plane pitch = 0 mod 32 banks, so a warp
+// whose 32 x-neighbours run over several rows / planes of the box still hits 32 different banks (a 40-word pitch
+// cost 2.4 wavefronts per LDS at config-3 angles).  int16: 96 shorts = 48 words with BY odd make both pitches
+// = 16 mod 32; a warp's run covers at most 17 words, so its continuation on the next row / plane lands in the
+// other half of the banks whatever the sign of the rotation (1.26 wavefronts per LDS against 1.75 for a 64-short
+// pitch, where the two lanes that straddle the row change share a bank half of the time).  The joint-histogram
+// kernels carry bins^2 counters beside the ring and use smaller boxes to keep their resident CTA count.
+#ifndef MIA_CFG_I16_STORE
+#define MIA_CFG_I16_STORE 96, 15, 13, 3, 2, false
 #endif
-#ifndef MIA_NST_I16
-#define MIA_NST_I16 2
+#ifndef MIA_CFG_I16_SSD
+#define MIA_CFG_I16_SSD 96, 15, 12, 2, 3, false
 #endif
-template <> struct BoxFor<int16_t> { using type = Box<MIA_BX_I16, MIA_BY_I16, MIA_BZ_I16>; };
-#ifndef MIA_BX_F32
-#define MIA_BX_F32 64     // 64 words: row and plane pitch = 0 mod 32 banks, so a warp whose 32 x-neighbours cross
-#define MIA_BY_F32 15     // rows / planes of the box still hits 32 different banks (pitch 40 cost 2.4 wavefronts
-#define MIA_BZ_F32 14     // per LDS at config-3 angles, ncu r01 prof_c3); 2 stages x 2 CTAs fill the 228 KB
+#ifndef MIA_CFG_I16_HIST
+#define MIA_CFG_I16_HIST 64, 16, 12, 2, 3, false
 #endif
-template <> struct BoxFor<float>   { using type = Box<MIA_BX_F32, MIA_BY_F32, MIA_BZ_F32>; };
-#ifndef MIA_BX_F32H       // joint-histogram kernels carry bins^2 counters per CTA next to the ring
-#define MIA_BX_F32H 64
-#define MIA_BY_F32H 14
-#define MIA_BZ_F32H 13
+#ifndef MIA_CFG_F32_STORE
+#define MIA_CFG_F32_STORE 64, 15, 14, 2, 2, false
 #endif
-using BoxF32Hist = Box<MIA_BX_F32H, MIA_BY_F32H, MIA_BZ_F32H>;
-#ifndef MIA_BX_I16H
-#define MIA_BX_I16H 64
-#define MIA_BY_I16H 16
-#define MIA_BZ_I16H 12
+#ifndef MIA_CFG_F32_SSD
+#define MIA_CFG_F32_SSD 64, 15, 14, 2, 2, false
 #endif
-using BoxI16Hist = Box<MIA_BX_I16H, MIA_BY_I16H, MIA_BZ_I16H>;
-template <typename TM> struct StagesFor { static constexpr int value = sizeof(TM) == 2 ? MIA_NST_I16 : 2; };
+#ifndef MIA_CFG_F32_HIST
+#define MIA_CFG_F32_HIST 64, 14, 13, 2, 2, true
+#endif
+template <int BX, int BY, int BZ, int NST_, int MINB_, bool PREFETCH_>
+struct TileCfgT {
+    using BOX = Box<BX, BY, BZ>;
+    static constexpr int NST = NST_, MINB = MINB_;
+    static constexpr bool PREFETCH = PREFETCH_;
+};
+template <typename TM, int METRIC> struct TileCfg;
+template <> struct TileCfg<int16_t, kNone> : TileCfgT<MIA_CFG_I16_STORE> {};   // 3-deep ring, 2 CTAs of 96 registers
+template <> struct TileCfg<int16_t, kSsd> : TileCfgT<MIA_CFG_I16_SSD> {};
+template <> struct TileCfg<int16_t, kHist> : TileCfgT<MIA_CFG_I16_HIST> {};
+template <> struct TileCfg<float, kNone> : TileCfgT<MIA_CFG_F32_STORE> {};
+template <> struct TileCfg<float, kSsd> : TileCfgT<MIA_CFG_F32_SSD> {};
+template <> struct TileCfg<float, kHist> : TileCfgT<MIA_CFG_F32_HIST> {};
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
@@ -230,18 +237,13 @@ void fill_tile(KParams &p)
     p.ntiles = (long long)p.ntx * p.nty * ((p.oz + kTZ - 1) / kTZ);
 }
 
-template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, class BOX>
+template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK>
 int launch_tile(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream_t s)
 {
-#ifndef MIA_MINB_I16M
-#define MIA_MINB_I16M 3
-#endif
-    constexpr int MINB = sizeof(TM) == 2 ? (METRIC == kNone ? 3 : MIA_MINB_I16M) : 2;
-    constexpr int NST = StagesFor<TM>::value;
-#ifndef MIA_PREFETCH_RULE
-#define MIA_PREFETCH_RULE (sizeof(TM) == 4 && METRIC == kHist)
-#endif
-    constexpr bool PREFETCH = MIA_PREFETCH_RULE;      // measured per kernel family, see tile_compute
+    using CFG = TileCfg<TM, METRIC>;
+    using BOX = typename CFG::BOX;
+    constexpr int NST = CFG::NST, MINB = CFG::MINB;
+    constexpr bool PREFETCH = CFG::PREFETCH;
     auto k = tile_kernel<TM, TF, TO, METRIC, STORE, VTK, BOX, NST, MINB, PREFETCH>;
     const size_t smem = TileSmem<TM, BOX, NST>::bytes(METRIC == kHist ? p.bins : 0);
     static std::mutex mu;
@@ -273,10 +275,11 @@ int launch_tile(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream
 
 
 // One (element type, box) attempt: fit test for host matrices, tensor map, launch.
-template <int METRIC, bool STORE, typename TM, class BOX>
+template <int METRIC, bool STORE, typename TM>
 int try_tile_box(int mode, const void *d_mov, const int mdims[3], const double *A_host, int n_mats, KParams p,
                  cudaStream_t s, bool &launched)
 {
+    using BOX = typename TileCfg<TM, METRIC>::BOX;
     launched = false;
     alignas(64) CUtensorMap map;
     for (int m = 0; A_host && m < n_mats; ++m)
@@ -287,8 +290,8 @@ int try_tile_box(int mode, const void *d_mov, const int mdims[3], const double *
     if (p.ntiles > 0x7fffffffLL) return MIA_OK;
     if ((long long)p.ox * p.oy * kTZ >= 0x7fffffffLL) return MIA_OK;   // in-tile plane offsets are 32-bit
     launched = true;
-    return mode == MIA_MODE_VTK ? launch_tile<TM, TM, TM, METRIC, STORE, true, BOX>(map, p, n_mats, s)
-                                : launch_tile<TM, TM, TM, METRIC, STORE, false, BOX>(map, p, n_mats, s);
+    return mode == MIA_MODE_VTK ? launch_tile<TM, TM, TM, METRIC, STORE, true>(map, p, n_mats, s)
+                                : launch_tile<TM, TM, TM, METRIC, STORE, false>(map, p, n_mats, s);
 }
 
 // Try the tile path for (dtype, mode); `launched` tells whether it took the call.  A_host may be null
@@ -298,16 +301,8 @@ int try_tile(int dtype, int mode, const void *d_mov, const int mdims[3], const d
              KParams p, cudaStream_t s, bool &launched)
 {
     launched = false;
-    if (dtype == MIA_F32) {
-        if constexpr (METRIC == kHist)
-            return try_tile_box<METRIC, STORE, float, BoxF32Hist>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
-        else
-            return try_tile_box<METRIC, STORE, float, BoxFor<float>::type>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
-    }
-    if constexpr (METRIC == kHist)
-        return try_tile_box<METRIC, STORE, int16_t, BoxI16Hist>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
-    else
-        return try_tile_box<METRIC, STORE, int16_t, BoxFor<int16_t>::type>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
+    if (dtype == MIA_F32) return try_tile_box<METRIC, STORE, float>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
+    return try_tile_box<METRIC, STORE, int16_t>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
 }
 
 }  // namespace
