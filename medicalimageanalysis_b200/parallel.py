@@ -8,6 +8,11 @@ and the partial ``{ssd, count}`` or joint histograms are combined by ``all_reduc
 (``gloo`` in the CPU tests).  The moving volume is replicated: ``A`` changes every iteration of a
 registration loop, and even config 5 (2.5 GB) is small next to 180 GB of HBM.
 
+Volumes too small to cut (config 3: 256^3 is 50 us of work per evaluation) shard over the 13 PROBES of an
+optimiser iteration instead: rank r evaluates probes ``[q0_r, q1_r)`` on a replicated pair and the
+13 costs are combined by one ``all_reduce(SUM)`` of a 13-vector that is zero outside each rank's share
+(``probe_bounds``, ``probe_parallel_costs``, ``register_rigid_probe_parallel``).
+
 Pure resampling needs no collective at all: the output stays sharded (``resample_slab``), or whole
 volumes are dealt out per rank (config 4, ``bench.py --gpus N``).
 
@@ -197,3 +202,107 @@ def register_rigid_sharded(fixed, moving, params0=None, cfg=None, group=None):
                               converged=bool(conv.value), n_reject=int(nrej.value), cost_history=hc[:iters.value],
                               param_history=hp[:iters.value], scale_history=hs[:iters.value],
                               evaluations=N_PROBES * int(iters.value), extra={"slab": (k0, k1), "world": world})
+
+
+# ---------------------------------------------------------------------------------------------------------
+# probe-parallel evaluation (small volumes)
+
+def probe_bounds(n_probes: int, world: int):
+    """``world + 1`` increasing probe indices; rank r evaluates ``[b[r], b[r+1])`` (sizes differ by at most 1,
+    ranks beyond the probe count get nothing)."""
+    n_probes, world = int(n_probes), int(world)
+    if n_probes < 0 or world < 1:
+        raise ValueError("need n_probes >= 0 and world >= 1")
+    return [(n_probes * r) // world for r in range(world)] + [n_probes]
+
+
+def probe_parallel_costs(evaluate_subset, probes, rank, world, group=None):
+    """Generic driver, also used by the CPU tests with the oracle as ``evaluate_subset``:
+    ``evaluate_subset(list_of_param_vectors) -> costs`` is called with this rank's share of ``probes``; returns
+    the full cost vector (float64 tensor) on every rank.  Adding zeros is exact, so the vector is bit-identical
+    on all ranks and to the single-process result."""
+    import torch
+    b = probe_bounds(len(probes), world)
+    q0, q1 = b[rank], b[rank + 1]
+    costs = torch.zeros(len(probes), dtype=torch.float64)
+    if q1 > q0:
+        costs[q0:q1] = torch.as_tensor(np.asarray(evaluate_subset(list(probes[q0:q1])), dtype=np.float64))
+    all_reduce_sum(costs, group=group)
+    return costs
+
+
+def register_rigid_probe_parallel(fixed, moving, params0=None, cfg=None, group=None):
+    """``registration.register_rigid`` with the 13 probes of every iteration dealt out over the ranks of
+    ``group``; fixed and moving are replicated (CUDA arrays on each rank's own device).
+
+    Per iteration: one fused launch over this rank's probes, MI from its own histograms, one ``all_reduce`` of
+    ``{cost[13], count[13]}`` (208 B, zero outside the rank's share), then the one-thread optimiser kernel on
+    every rank -- identical inputs, so all ranks walk the same trajectory.  Returns the same
+    ``RegistrationResult`` everywhere."""
+    import torch
+
+    from . import _lib, kernels
+    from .registration import N_PROBES, RegistrationConfig, RegistrationResult, _intensity_range
+    dist = _dist()
+    lib = _lib.load()
+    cfg = cfg or RegistrationConfig()
+    on = dist.is_available() and dist.is_initialized()
+    rank = dist.get_rank(group) if on else 0
+    world = dist.get_world_size(group) if on else 1
+    params0 = np.zeros(6) if params0 is None else np.asarray(params0, dtype=np.float64)
+    dev = fixed.array.device
+    center = np.asarray(fixed.compute_center(), dtype=np.float64)
+    p2w = G.index_to_physical(fixed.grid, "itk")
+    w2p = G.physical_to_index(moving.grid, "itk")
+    if cfg.metric not in ("ssd", "mi"):
+        raise ValueError("metric must be 'ssd' or 'mi'")
+    is_ssd = cfg.metric == "ssd"
+    b = probe_bounds(N_PROBES, world)
+    q0, q1 = b[rank], b[rank + 1]
+    nloc = q1 - q0
+    ws = kernels.MetricWorkspace(dev, n_mats=max(nloc, 1), bins=cfg.bins)
+    d_A = torch.zeros((N_PROBES, 3, 4), dtype=torch.float64, device=dev)
+    cost = torch.zeros(N_PROBES, dtype=torch.float64, device=dev)
+    count = torch.zeros(N_PROBES, dtype=torch.int64, device=dev)
+    state = torch.zeros(int(lib.mia_optimizer_state_bytes()), dtype=torch.uint8, device=dev)
+    if not is_ssd:
+        frange = cfg.frange or _intensity_range(fixed.array)
+        mrange = cfg.mrange or _intensity_range(moving.array)
+
+    def stream():
+        return ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+    with torch.cuda.device(dev):
+        _lib.check(lib.mia_optimizer_init(state.data_ptr(), _lib.darr(params0), _lib.darr(center),
+                                          _lib.darr(p2w.ravel()), _lib.darr(w2p.ravel()), cfg.rot_step_deg,
+                                          cfg.trans_step_mm, cfg.min_step_scale, 0 if is_ssd else 1,
+                                          d_A.data_ptr(), stream()))
+        for _ in range(cfg.iterations):
+            cost.zero_(); count.zero_()
+            if nloc > 0:
+                mine = d_A[q0:q1]
+                if is_ssd:
+                    v, c = kernels.resample_ssd(fixed.array, moving.array, d_A=mine, mode=cfg.mode, ws=ws)
+                else:
+                    h, c = kernels.resample_jointhist(fixed.array, moving.array, frange, mrange, bins=cfg.bins,
+                                                      d_A=mine, mode=cfg.mode, ws=ws)
+                    v = kernels.mi_from_hist(h, out=ws.mi[:nloc])
+                cost[q0:q1] = v
+                count[q0:q1] = c
+            all_reduce_sum(cost, count, group=group)
+            _lib.check(lib.mia_optimizer_step(state.data_ptr(), cost.data_ptr(), count.data_ptr(),
+                                              1 if is_ssd else 0, d_A.data_ptr(), stream()))
+        n = min(cfg.iterations, 4096)
+        params = (ctypes.c_double * 6)()
+        scale = ctypes.c_double()
+        iters, conv, nrej = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        hc = np.zeros(n); hp = np.zeros((n, 6)); hs = np.zeros(n)
+        dp = ctypes.POINTER(ctypes.c_double)
+        _lib.check(lib.mia_optimizer_read(state.data_ptr(), params, ctypes.byref(scale), ctypes.byref(iters),
+                                          ctypes.byref(conv), ctypes.byref(nrej), hc.ctypes.data_as(dp),
+                                          hp.ctypes.data_as(dp), hs.ctypes.data_as(dp), n, stream()))
+    p = np.array(list(params))
+    return RegistrationResult(params=p, matrix=G.params_to_matrix(p, center), iterations=int(iters.value),
+                              converged=bool(conv.value), n_reject=int(nrej.value), cost_history=hc[:iters.value],
+                              param_history=hp[:iters.value], scale_history=hs[:iters.value],
+                              evaluations=N_PROBES * int(iters.value), extra={"probes": (q0, q1), "world": world})

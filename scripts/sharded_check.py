@@ -62,12 +62,28 @@ def main():
     same_path = bool(np.array_equal(single.scale_history, shard.scale_history))
     cost_rel = float(np.max(np.abs(single.cost_history - shard.cost_history) / np.abs(single.cost_history)))
     par_abs = float(np.max(np.abs(single.params - shard.params)))
-    flags = torch.tensor([int(ok_hist), int(same_path), int(ssd_rel < 1e-8), int(cost_rel < 1e-7)], device=dev)
+    # probe-parallel (13 probes dealt out over the ranks, volumes replicated): bit-identical to one GPU
+    pp = {}
+    for metric in ("ssd", "mi"):
+        cfgp = RegistrationConfig(metric=metric, iterations=30, bins=64, graph_iters=0)
+        one = R.register_rigid(fi, mi, cfg=cfgp)
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        t0 = time.perf_counter()
+        par = P.register_rigid_probe_parallel(fi, mi, cfg=cfgp)
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        pp[metric] = {"identical": bool(np.array_equal(one.cost_history, par.cost_history)
+                                        and np.array_equal(one.params, par.params)),
+                      "iters_per_s": par.iterations / (time.perf_counter() - t0)}
+    flags = torch.tensor([int(ok_hist), int(same_path), int(ssd_rel < 1e-8), int(cost_rel < 1e-7),
+                          int(pp["ssd"]["identical"]), int(pp["mi"]["identical"])], device=dev)
     dist.all_reduce(flags, op=dist.ReduceOp.MIN)
     if rank == 0:
         print(json.dumps({"world": world, "hist_count_bit_identical": bool(flags[0]), "same_trajectory": bool(flags[1]),
                           "ssd_rel_err": ssd_rel, "cost_rel_err": cost_rel, "param_abs_err": par_abs,
-                          "sharded_iters_per_s": shard.iterations / dt, "slab": shard.extra["slab"]}), flush=True)
+                          "sharded_iters_per_s": shard.iterations / dt, "slab": shard.extra["slab"],
+                          "probe_parallel": pp}), flush=True)
     dist.barrier()
     dist.destroy_process_group()
     if not bool(flags.min()):

@@ -33,6 +33,26 @@ def test_world1_sharded_equals_plain(cuda_device, metric):
     Data.clear()
 
 
+@pytest.mark.parametrize("metric", ["ssd", "mi"])
+def test_world1_probe_parallel_equals_plain(cuda_device, metric):
+    shape, sp = (24, 48, 64), (1.5, 1.5, 2.0)
+    Data.clear()
+    fixed = make_phantom(shape, "CT", seed=3, spacing=sp).astype(np.float32)
+    f = CreateImageFromMask(fixed, (-48.0, -36.0, -24.0), sp, "fixed", device=cuda_device).add_image()
+    M = G.params_to_matrix([2.0, -1.0, 1.5, 2.0, 1.0, -1.0], f.compute_center())
+    moving = make_phantom(shape, "CT" if metric == "ssd" else "MR", seed=3, spacing=sp,
+                          world_matrix=np.linalg.inv(M)).astype(np.float32)
+    m = CreateImageFromMask(moving, (-48.0, -36.0, -24.0), sp, "moving", device=cuda_device).add_image()
+    cfg = RegistrationConfig(metric=metric, iterations=12, bins=32, graph_iters=0)
+    a = R.register_rigid(f, m, cfg=cfg)
+    b = P.register_rigid_probe_parallel(f, m, cfg=cfg)
+    assert a.iterations == b.iterations == 12 and b.extra["probes"] == (0, 13)
+    assert np.array_equal(a.scale_history, b.scale_history)
+    assert np.array_equal(a.cost_history, b.cost_history)
+    assert np.array_equal(a.params, b.params)
+    Data.clear()
+
+
 def test_resample_slabs_concatenate_to_the_whole(cuda_device):
     from medicalimageanalysis_b200 import kernels
     shape, sp = (40, 48, 64), (1.0, 1.0, 2.0)

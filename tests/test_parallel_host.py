@@ -100,3 +100,67 @@ def test_gloo_sharded_metrics_equal_the_whole(world):
         assert cnt[i] == n and abs(ssd[i] - want) <= 1e-12 * want
         H, hn = native.joint_hist(fixed, moving, A, 16, fr, fr, "itk")
         assert hc[i] == hn and np.array_equal(h[i], H.astype(np.int64))
+
+
+# ---------------------------------------------------------------------------------------------------------
+# probe-parallel evaluation (small volumes): the 13 probes of an iteration dealt out over the ranks
+
+def test_probe_bounds_partition():
+    for n in (0, 1, 5, 13):
+        for world in (1, 2, 3, 4, 8, 16):
+            b = P.probe_bounds(n, world)
+            assert b[0] == 0 and b[-1] == n and len(b) == world + 1
+            sizes = [b[i + 1] - b[i] for i in range(world)]
+            assert all(s >= 0 for s in sizes) and max(sizes) - min(sizes) <= 1
+
+
+def _probe_case():
+    from medicalimageanalysis_b200.registration import RegistrationConfig, params_to_index_matrix
+    shape, sp = (16, 20, 24), (1.0, 1.0, 1.5)
+    g = G.Grid((shape[2], shape[1], shape[0]), sp, tuple(-0.5 * np.array(sp) * np.array(shape[::-1])))
+    center = tuple(np.asarray(g.origin) + 0.5 * (np.asarray(g.dims) - 1) * np.asarray(g.spacing))
+    fixed = make_phantom(shape, "CT", seed=5, spacing=sp)
+    moving = make_phantom(shape, "CT", seed=5, spacing=sp,
+                          world_matrix=np.linalg.inv(G.params_to_matrix((1.5, -1.0, 2.0, 1.0, -0.5, 0.8), center)))
+    p2w, w2p = G.index_to_physical(g, "itk"), G.physical_to_index(g, "itk")
+
+    def evaluate(plist):
+        out = []
+        for prm in plist:
+            ssd, n = native.reslice_ssd(fixed, moving, params_to_index_matrix(prm, center, p2w, w2p), "itk")
+            out.append(ssd / max(n, 1))
+        return out
+    return evaluate, RegistrationConfig(metric="ssd", iterations=6)
+
+
+def _probe_worker(rank, world, port, q):
+    from medicalimageanalysis_b200.registration import host_optimizer
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        evaluate, cfg = _probe_case()
+        res = host_optimizer(lambda pl: P.probe_parallel_costs(evaluate, pl, rank, world).numpy(), np.zeros(6), cfg)
+        q.put((rank, res.params, res.cost_history))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_gloo_probe_parallel_walks_the_single_process_trajectory(world):
+    from medicalimageanalysis_b200.registration import host_optimizer
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_probe_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=180) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    evaluate, cfg = _probe_case()
+    want = host_optimizer(evaluate, np.zeros(6), cfg)
+    for _, params, hist in got:                      # every rank, bit for bit (adding zeros is exact)
+        assert np.array_equal(params, want.params) and np.array_equal(hist, want.cost_history)
+    assert want.cost_history[-1] < want.cost_history[0]
