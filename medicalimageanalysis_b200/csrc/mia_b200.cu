@@ -15,6 +15,7 @@
 #include "mia_kernels.cuh"
 #include "mia_optimizer.cuh"
 #include "mia_tile.cuh"
+#include "mia_tile_multi.cuh"
 
 using namespace mia;
 
@@ -294,6 +295,87 @@ int try_tile_box(int mode, const void *d_mov, const int mdims[3], const double *
                                 : launch_tile<TM, TM, TM, METRIC, STORE, false>(map, p, n_mats, s);
 }
 
+// Multi-matrix SSD (mia_tile_multi.cuh): one box per tile position for all matrices of the launch, one CTA per SM
+// with G consumer groups.  (ring depth, groups) per element type; tuning builds override with -D.
+#ifndef MIA_MULTI_I16
+#define MIA_MULTI_I16 4, 3
+#endif
+#ifndef MIA_MULTI_F32
+#define MIA_MULTI_F32 3, 3
+#endif
+template <int NST_, int G_> struct MultiCfgT { static constexpr int NST = NST_, G = G_; };
+template <typename TM> struct MultiCfg;
+template <> struct MultiCfg<int16_t> : MultiCfgT<MIA_MULTI_I16> {};
+template <> struct MultiCfg<float> : MultiCfgT<MIA_MULTI_F32> {};
+
+template <typename TM, bool VTK>
+int launch_multi(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream_t s)
+{
+    using BOX = typename TileCfg<TM, kSsd>::BOX;
+    constexpr int NST = MultiCfg<TM>::NST, G = MultiCfg<TM>::G;
+    constexpr int threads = 32 * (kConsumerWarps * G + 1);
+    auto k = tile_multi_kernel<TM, TM, VTK, BOX, NST, G>;
+    const size_t smem = MultiSmem<TM, BOX, NST>::kBytes;
+    static std::mutex mu;
+    static std::map<int, int> occ;                         // device -> resident CTAs per SM
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    int nb = 0;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        auto it = occ.find(dev);
+        if (it == occ.end()) {
+            CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k, threads, smem));
+            if (nb < 1) return fail(MIA_ERR_UNSUPPORTED, "multi-matrix tile kernel does not fit on this device (%zu B smem)", smem);
+            occ[dev] = nb;
+        } else {
+            nb = it->second;
+        }
+    }
+    long long gx = (long long)sm_count() * nb;
+    if (gx > p.ntiles) gx = p.ntiles;
+    if (gx > kMaxGridX) gx = kMaxGridX;
+    k<<<dim3((unsigned)gx, 1, 1), threads, smem, s>>>(map, p, n_mats);
+    CUDA_TRY(cudaGetLastError());
+    g_last_path = 2;
+    return MIA_OK;
+}
+
+bool multi_path_disabled()
+{
+    static const bool off = [] { const char *e = getenv("MIA_NO_MULTI"); return e && *e && *e != '0'; }();
+    return off;
+}
+
+template <typename TM>
+int try_multi_t(int mode, const void *d_mov, const int mdims[3], const double *A_host, int n_mats, KParams p,
+                cudaStream_t s, bool &launched)
+{
+    using BOX = typename TileCfg<TM, kSsd>::BOX;
+    launched = false;
+    alignas(64) CUtensorMap map;
+    for (int m = 0; A_host && m < n_mats; ++m)
+        if (!box_fits<TM, BOX>(A_host + 12 * m)) return MIA_OK;
+    if (!make_tensor_map<TM, BOX>(&map, d_mov, mdims)) return MIA_OK;
+    fill_tile(p);
+    p.magic_fold = 0u - kMagicBits * (unsigned)((BOX::kY + 1) * BOX::kX + 1) * (unsigned)sizeof(TM);
+    if (p.ntiles > 0x7fffffffLL) return MIA_OK;
+    if ((long long)p.ox * p.oy * kTZ >= 0x7fffffffLL) return MIA_OK;
+    launched = true;
+    return mode == MIA_MODE_VTK ? launch_multi<TM, true>(map, p, n_mats, s) : launch_multi<TM, false>(map, p, n_mats, s);
+}
+
+// SSD of 2..kMaxMulti matrices without a stored output; p.dA is set (metric_common stages host matrices).
+int try_multi(int dtype, int mode, const void *d_mov, const int mdims[3], const double *A_host, int n_mats, KParams p,
+              cudaStream_t s, bool &launched)
+{
+    launched = false;
+    if (n_mats < 2 || n_mats > kMaxMulti || !p.dA || tile_path_disabled() || multi_path_disabled()) return MIA_OK;
+    if (dtype == MIA_F32) return try_multi_t<float>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
+    return try_multi_t<int16_t>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
+}
+
 // Try the tile path for (dtype, mode); `launched` tells whether it took the call.  A_host may be null
 // (device matrices: the kernel classifies every tile itself and falls back per tile).
 template <int METRIC, bool STORE>
@@ -421,6 +503,10 @@ int mia_resample_ssd(const void *d_mov, int mov_dtype, const int mdims[3], const
     g_last_path = 0;
     if (mov_dtype == fixed_dtype) {
         bool launched = false;
+        if (!d_out) {
+            const int mrc = try_multi(mov_dtype, mode, d_mov, mdims, d_A ? nullptr : A, n_mats, p, s, launched);
+            if (launched) return mrc;
+        }
         const int trc = d_out ? try_tile<kSsd, true>(mov_dtype, mode, d_mov, mdims, d_A ? nullptr : A, n_mats, p, s, launched)
                               : try_tile<kSsd, false>(mov_dtype, mode, d_mov, mdims, d_A ? nullptr : A, n_mats, p, s, launched);
         if (launched) return trc;

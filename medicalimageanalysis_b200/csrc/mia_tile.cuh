@@ -137,8 +137,63 @@ __host__ __device__ inline Reach tile_reach(const double *A)
     return r;
 }
 
-// Classify one tile and choose its box.  Shared by the device producer and the host (launch heuristics,
-// unit tests).  `closed` only matters for ties and is folded into the conservative tests below.
+struct TileAabb {           // bounding box of one tile in moving index space, padded and clipped to the volume
+    double c0[3];           // continuous moving index of the tile's first voxel
+    int lo[3], hi[3];       // first box element needed, one past the last (upper tap included)
+    bool outside, interior;
+};
+
+__host__ __device__ inline TileAabb tile_aabb(const double *A, const Reach &r, int i0, int j0, int k0, int nx, int ny, int nz)
+{
+    TileAabb t;
+    t.c0[0] = ((A[3] + (double)k0 * A[2]) + (double)j0 * A[1]) + (double)i0 * A[0];
+    t.c0[1] = ((A[7] + (double)k0 * A[6]) + (double)j0 * A[5]) + (double)i0 * A[4];
+    t.c0[2] = ((A[11] + (double)k0 * A[10]) + (double)j0 * A[9]) + (double)i0 * A[8];
+    const int n[3] = {nx, ny, nz};
+    t.outside = false;
+    t.interior = true;
+    for (int a = 0; a < 3; ++a) {
+        t.lo[a] = t.hi[a] = 0;
+        const double lo = t.c0[a] + r.neg[a], hi = t.c0[a] + r.pos[a];
+        if (!(hi >= -0.5) || !(lo <= (double)n[a] - 0.5)) { t.outside = true; continue; }   // NaN -> outside
+        if (!(lo >= 0.0 && hi <= (double)(n[a] - 1))) t.interior = false;
+        const double top = (double)(n[a] - 1);
+        double lc = lo < 0.0 ? 0.0 : (lo > top ? top : lo);
+        double hc = hi < 0.0 ? 0.0 : (hi > top ? top : hi);
+        lc -= 1.0e-3;                      // float32 thread coordinates may stray ~1e-6 beyond the AABB
+        hc += 1.0e-3;
+        t.lo[a] = (int)floor(lc);
+        t.hi[a] = (int)floor(hc) + 2;
+    }
+    return t;
+}
+
+// Does the tile's AABB fit a box whose element [0][0][0] is moving index b?
+template <class BOX>
+__host__ __device__ inline bool aabb_fits(const TileAabb &t, int bx, int by, int bz)
+{
+    return t.lo[0] >= bx && t.lo[1] >= by && t.lo[2] >= bz && t.hi[0] - bx <= BOX::kX && t.hi[1] - by <= BOX::kY &&
+           t.hi[2] - bz <= BOX::kZ;
+}
+
+// The record the consumers need for a tile whose box origin has been chosen.
+template <class BOX>
+__host__ __device__ inline TileInfo tile_place(const TileAabb &bb, int bx, int by, int bz)
+{
+    TileInfo t;
+    t.bx = bx; t.by = by; t.bz = bz;
+    t.cls = bb.outside ? kOutside : (!aabb_fits<BOX>(bb, bx, by, bz) ? kNoFit : (bb.interior ? kInterior : kBorder));
+    t.rx = t.ry = t.rz = 0;
+    if (t.cls == kInterior || t.cls == kBorder) {       // |c0 - b| is a few box widths at most here
+        t.rx = (long long)floor((bb.c0[0] - (double)bx) * 4294967296.0);
+        t.ry = (long long)floor((bb.c0[1] - (double)by) * 4294967296.0);
+        t.rz = (long long)floor((bb.c0[2] - (double)bz) * 4294967296.0);
+    }
+    return t;
+}
+
+// Classify one tile and choose its own box.  Shared by the device producer and the host (launch heuristics,
+// unit tests).
 // TMA constraint measured on B200 (tests/cuda/tma_probe3.cu): with INTERLEAVE_NONE the innermost box
 // coordinate times the element size must be a multiple of 16 bytes, otherwise the copy raises "illegal
 // instruction".  The box origin along x is therefore rounded down to `xalign` (= 16 / sizeof(element)) voxels.
@@ -146,37 +201,8 @@ template <class BOX>
 __host__ __device__ inline TileInfo classify_tile(const double *A, const Reach &r, int i0, int j0, int k0,
                                                   int nx, int ny, int nz, int xalign)
 {
-    TileInfo t;
-    const double c0[3] = {((A[3] + (double)k0 * A[2]) + (double)j0 * A[1]) + (double)i0 * A[0],
-                          ((A[7] + (double)k0 * A[6]) + (double)j0 * A[5]) + (double)i0 * A[4],
-                          ((A[11] + (double)k0 * A[10]) + (double)j0 * A[9]) + (double)i0 * A[8]};
-    const int n[3] = {nx, ny, nz};
-    const int B[3] = {BOX::kX, BOX::kY, BOX::kZ};
-    int b[3] = {0, 0, 0};
-    bool outside = false, interior = true, fits = true;
-    for (int a = 0; a < 3; ++a) {
-        const double lo = c0[a] + r.neg[a], hi = c0[a] + r.pos[a];
-        if (!(hi >= -0.5) || !(lo <= (double)n[a] - 0.5)) { outside = true; continue; }   // NaN -> outside
-        if (!(lo >= 0.0 && hi <= (double)(n[a] - 1))) interior = false;
-        const double top = (double)(n[a] - 1);
-        double lc = lo < 0.0 ? 0.0 : (lo > top ? top : lo);
-        double hc = hi < 0.0 ? 0.0 : (hi > top ? top : hi);
-        lc -= 1.0e-3;                      // float32 thread coordinates may stray ~1e-6 beyond the AABB
-        hc += 1.0e-3;
-        const double fh = floor(hc);
-        b[a] = (int)floor(lc);
-        if (a == 0) b[a] &= ~(xalign - 1);          // two's complement: rounds toward -inf for negatives too
-        if (fh + 2.0 - (double)b[a] > (double)B[a]) fits = false;
-    }
-    t.bx = b[0]; t.by = b[1]; t.bz = b[2];
-    t.cls = outside ? kOutside : (!fits ? kNoFit : (interior ? kInterior : kBorder));
-    t.rx = t.ry = t.rz = 0;
-    if (t.cls == kInterior || t.cls == kBorder) {       // |c0 - b| is a few box widths at most here
-        t.rx = (long long)floor((c0[0] - (double)b[0]) * 4294967296.0);
-        t.ry = (long long)floor((c0[1] - (double)b[1]) * 4294967296.0);
-        t.rz = (long long)floor((c0[2] - (double)b[2]) * 4294967296.0);
-    }
-    return t;
+    const TileAabb bb = tile_aabb(A, r, i0, j0, k0, nx, ny, nz);
+    return tile_place<BOX>(bb, bb.lo[0] & ~(xalign - 1), bb.lo[1], bb.lo[2]);   // & rounds toward -inf (two's complement)
 }
 
 
@@ -319,7 +345,12 @@ __device__ __forceinline__ void load_fixed(float (&fv)[kTZ], const TF *fp, int n
 // output voxel column (i0 + lane, j0 + warp), as 4 packed pairs.  BORDER adds the inside test and the
 // coordinate clamp (== VTK/ITK index clamp: the clamped coordinate has weight 0 on the tap beyond the edge,
 // which TMA zero-filled); interior tiles need neither.
-template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, bool BORDER, class BOX, bool PREFETCH>
+// FX says who owns the fixed-image registers fv[]: kFxLoadHere (loaded at the top from nfp / nk), kFxPrefetchNext
+// (valid on entry, each pair refills its two registers with the NEXT tile's values from nfp / nk) or kFxKeep
+// (valid on entry, left alone: the multi-matrix kernel reuses them for every matrix of the tile).
+enum { kFxLoadHere = 0, kFxPrefetchNext = 1, kFxKeep = 2 };
+
+template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, bool BORDER, class BOX, int FX>
 __device__ __forceinline__ void tile_compute(const KParams &p, const unsigned char *stage, const TileInfo &ti,
                                              const ThreadGeom &g, int i0, int j0, int k0, int lane, int warp,
                                              double &acc, unsigned &cnt, unsigned *s_hist, float (&fv)[kTZ],
@@ -361,12 +392,11 @@ __device__ __forceinline__ void tile_compute(const KParams &p, const unsigned ch
     TO *out = static_cast<TO *>(p.out) + gofs;
     const TO bgv = tile_to_out<TO, VTK>(p.background);
 
-    // fv[] holds this thread's 8 fixed-image values of THIS tile.  PREFETCH: they were fetched while the previous
-    // tile was computed, and each pair reloads its two registers with the next tile's values (nfp / nk) as soon
-    // as it has used them, so the global-load latency hides behind a whole tile of arithmetic.  Otherwise they
-    // are loaded here (nfp / nk then describe this tile): the 72-register int16 kernels spill with the longer
-    // live ranges, and lose more than the latency costs them.
-    if (METRIC != kNone && !PREFETCH) load_fixed<TF>(fv, nfp, nk, plane);
+    // fv[] holds this thread's 8 fixed-image values of THIS tile.  kFxPrefetchNext: they were fetched while the
+    // previous tile was computed, and each pair reloads its two registers with the next tile's values as soon as
+    // it has used them, so the global-load latency hides behind a whole tile of arithmetic.  kFxLoadHere: loaded
+    // now -- the 72-register int16 kernels spill with the longer live ranges and lose more than the latency costs.
+    if (METRIC != kNone && FX == kFxLoadHere) load_fixed<TF>(fv, nfp, nk, plane);
     const f32x2 ax2 = pk(g.a2x, g.a2x), ay2 = pk(g.a2y, g.a2y), az2 = pk(g.a2z, g.a2z);
     const f32x2 fx2 = pk(fx, fx), fy2 = pk(fy, fy), fz2 = pk(fz, fz);
     const f32x2 magic2 = pk(kMagic, kMagic);
@@ -441,7 +471,7 @@ __device__ __forceinline__ void tile_compute(const KParams &p, const unsigned ch
             if (live0 && in0) red_shared_inc(h0);
             if (live1 && in1) red_shared_inc(h1);
         }
-        if (METRIC != kNone && PREFETCH) {
+        if (METRIC != kNone && FX == kFxPrefetchNext) {
             asm("" : "+l"(nfp));                     // keep ONE stepped 64-bit pointer (2 instructions per load)
             fv[kp] = kp < nk ? (float)__ldg(nfp) : 0.0f;
             nfp += plane;
@@ -631,10 +661,10 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ KP
             const TileInfo ti = infos[n & 63];
             const unsigned char *stage = tsm + L::kStageBytes * s;
             if (ti.cls == kInterior) {
-                tile_compute<TM, TF, TO, METRIC, STORE, VTK, false, BOX, PREFETCH>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt, s_hist,
+                tile_compute<TM, TF, TO, METRIC, STORE, VTK, false, BOX, PREFETCH ? kFxPrefetchNext : kFxLoadHere>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt, s_hist,
                                                                          fv, nfp, nk);
             } else if (ti.cls == kBorder) {
-                tile_compute<TM, TF, TO, METRIC, STORE, VTK, true, BOX, PREFETCH>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt, s_hist,
+                tile_compute<TM, TF, TO, METRIC, STORE, VTK, true, BOX, PREFETCH ? kFxPrefetchNext : kFxLoadHere>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt, s_hist,
                                                                         fv, nfp, nk);
             } else {
                 if (STORE || ti.cls == kNoFit)

@@ -54,7 +54,10 @@ def test_ssd_batched_equals_single_and_is_deterministic(cuda_device):
     assert torch.equal(s2, s1) and torch.equal(c2, c1)            # device matrices == host matrices
     for i in range(13):
         si, ci = kernels.resample_ssd(f, m, A=A[i])
-        assert float(si[0]) == float(s1[i]) and int(ci[0]) == int(c1[i])
+        # the batched launch shares one box per tile between the matrices (mia_tile_multi.cuh); these 13 are
+        # unrelated, so many tiles of many matrices miss the shared box and take the per-voxel gather, whose
+        # float64-row-origin arithmetic differs from the tile arithmetic in the last float32 bits
+        assert abs(float(si[0]) - float(s1[i])) <= 1e-7 * float(s1[i]) and int(ci[0]) == int(c1[i])
         want, n = native.reslice_ssd(fixed, moving, A[i], "itk")
         assert abs(float(s1[i]) - want) <= 1e-5 * want and abs(int(c1[i]) - n) <= 2
 

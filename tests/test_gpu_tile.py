@@ -21,6 +21,9 @@ def last_path():
     return int(_lib.load().mia_debug_last_path())
 
 
+MULTI = 2          # mia_tile_multi.cuh
+
+
 def grid_of(shape, sp):
     return G.Grid((shape[2], shape[1], shape[0]), sp, tuple(-0.5 * np.array(sp) * np.array(shape[::-1])))
 
@@ -128,7 +131,7 @@ def test_tile_metrics_match_oracle(cuda_device, modality):
     f, m = torch.from_numpy(fixed).to(cuda_device), torch.from_numpy(moving).to(cuda_device)
     ws = kernels.MetricWorkspace(cuda_device, n_mats=13, bins=64)
     s, c = kernels.resample_ssd(f, m, A=A, ws=ws)
-    assert last_path() == TILE
+    assert last_path() == MULTI           # 13 unrelated matrices: one shared box, per-tile gather for the misfits
     fr = (float(fixed.min()), float(fixed.max()))
     mr = (float(moving.min()), float(moving.max()))
     s, c = s.cpu().numpy().copy(), c.cpu().numpy().copy()
@@ -164,3 +167,63 @@ def test_tile_ssd_store_equals_plain_resample_and_is_deterministic(cuda_device):
     for _ in range(3):
         s2, _ = kernels.resample_ssd(f, m, A=A, mode="itk")
         assert float(s2[0]) == s0
+
+
+@pytest.mark.parametrize("dtype", [np.int16, np.float32])
+@pytest.mark.parametrize("mode", ["itk", "vtk"])
+def test_multi_matrix_ssd_equals_one_matrix_launches(cuda_device, dtype, mode):
+    """The 13 probes of an optimiser iteration share one box per tile (csrc/mia_tile_multi.cuh).  Every voxel
+    value is computed by the same tile_compute as in the one-matrix kernel, so counts are equal and sums agree
+    to summation-order rounding; the oracle pins both."""
+    from medicalimageanalysis_b200.registration import probe_params
+    shape, sp = (56, 72, 96), (1.0, 1.0, 1.5)
+    g = grid_of(shape, sp)
+    fixed = make_phantom(shape, "CT", seed=7, spacing=sp).astype(dtype)
+    moving = make_phantom(shape, "CT", seed=7, spacing=sp,
+                          world_matrix=np.linalg.inv(G.params_to_matrix([2, -3, 2.5, 3, -2, 1.5], (0, 0, 0)))).astype(dtype)
+    f, m = torch.from_numpy(fixed).to(cuda_device), torch.from_numpy(moving).to(cuda_device)
+    for scale in (1.0, 4.0):                       # probe offsets 0.5 and 2 (degrees / mm)
+        probes = probe_params(np.array([1.5, -2.5, 2.0, 2.0, -1.0, 1.0]), scale, np.array([0.5] * 6))
+        A = np.stack([G.compose_index_matrix(g, g, G.params_to_matrix(q, (0, 0, 0))) for q in probes])
+        for use_dev in (False, True):
+            ws = kernels.MetricWorkspace(cuda_device, n_mats=13)
+            if use_dev:
+                s, c = kernels.resample_ssd(f, m, d_A=torch.from_numpy(A).to(cuda_device), mode=mode, ws=ws)
+            else:
+                s, c = kernels.resample_ssd(f, m, A=A, mode=mode, ws=ws)
+            assert last_path() == MULTI
+            s, c = s.cpu().numpy().copy(), c.cpu().numpy().copy()
+            s2, c2 = kernels.resample_ssd(f, m, A=A, mode=mode, ws=ws)        # workspace reuse: ticket self-reset
+            assert np.array_equal(s2.cpu().numpy(), s) and np.array_equal(c2.cpu().numpy(), c)
+            for i in range(13):
+                s1, c1 = kernels.resample_ssd(f, m, A=A[i], mode=mode)
+                assert last_path() == TILE
+                assert int(c1[0]) == int(c[i])
+                # probes half a voxel apart share every box: identical voxel values, summation order only; at 2
+                # voxels / degrees some tiles of some probes miss the shared box and take the per-voxel gather
+                # (float64 row origin: last-bit differences in float32)
+                assert abs(float(s1[0]) - float(s[i])) <= (1e-12 if scale == 1.0 else 1e-7) * float(s1[0])
+            for i in (0, 5, 12):
+                want, n = native.reslice_ssd(fixed, moving, A[i], mode)
+                assert abs(int(c[i]) - n) <= 2 and abs(float(s[i]) - want) <= 1e-5 * want
+
+
+def test_multi_matrix_handles_outside_and_ragged(cuda_device):
+    """Matrices that push the tile outside the volume, a ragged output lattice and 2 / 16 matrices per launch."""
+    shape, sp = (19, 45, 70), (1.0, 1.0, 2.0)
+    g = grid_of(shape, sp)
+    fixed = make_phantom(shape, "CT", seed=9, spacing=sp)
+    moving = make_phantom(shape, "CT", seed=10, spacing=sp)
+    mov = np.ascontiguousarray(np.pad(moving, ((0, 0), (0, 0), (0, 2))))      # nx = 72: 16-byte row pitch
+    gm = G.Grid((72, 45, 19), sp, g.origin)
+    f, m = torch.from_numpy(fixed).to(cuda_device), torch.from_numpy(mov).to(cuda_device)
+    for nm in (2, 16):
+        rng = np.random.default_rng(nm)
+        prm = [np.concatenate([rng.uniform(-2, 2, 3), rng.uniform(-1, 1, 3) * (40 if i % 3 == 2 else 2)]) for i in range(nm)]
+        A = np.stack([G.compose_index_matrix(g, gm, G.params_to_matrix(q, (0, 0, 0))) for q in prm])
+        s, c = kernels.resample_ssd(f, m, A=A)
+        assert last_path() == MULTI
+        for i in range(nm):
+            want, n = native.reslice_ssd(fixed, mov, A[i], "itk")
+            assert abs(int(c[i]) - n) <= 2
+            assert abs(float(s[i]) - want) <= 1e-5 * max(want, 1.0)
