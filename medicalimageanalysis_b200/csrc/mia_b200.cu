@@ -296,12 +296,14 @@ int try_tile_box(int mode, const void *d_mov, const int mdims[3], const double *
 }
 
 // Multi-matrix SSD (mia_tile_multi.cuh): one box per tile position for all matrices of the launch, one CTA per SM
-// with G consumer groups.  (ring depth, groups) per element type; tuning builds override with -D.
+// with G consumer groups.  (ring depth, groups) per element type; tuning builds override with -D.  Measured per
+// evaluation, 13 probes (int16 512x512x100 / float32 256^3): one matrix per CTA 66.8 / 43.7 us; G = 1: 76.7 / 47.7;
+// G = 2: 59.8 / 39.1; G = 3: 64.1 / 39.8 (25 warps put 7 on one scheduler: 72 registers, spills).
 #ifndef MIA_MULTI_I16
-#define MIA_MULTI_I16 4, 3
+#define MIA_MULTI_I16 4, 2
 #endif
 #ifndef MIA_MULTI_F32
-#define MIA_MULTI_F32 3, 3
+#define MIA_MULTI_F32 3, 2
 #endif
 template <int NST_, int G_> struct MultiCfgT { static constexpr int NST = NST_, G = G_; };
 template <typename TM> struct MultiCfg;

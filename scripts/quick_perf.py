@@ -50,6 +50,13 @@ ws = kernels.MetricWorkspace(dev, n_mats=13, bins=64)
 fr, mr = (float(f1.min()), float(f1.max())), (float(m1.min()), float(m1.max()))
 res["c1_ssd_i16"] = timed(lambda: kernels.resample_ssd(f1, m1, A=A1, mode="itk", ws=ws))
 res["c1_hist_i16"] = timed(lambda: kernels.resample_jointhist(f1, m1, fr, mr, bins=64, A=A1, mode="itk", ws=ws))
+# 13 probes around one pose, device matrices (one registration iteration on int16 data)
+rng = np.random.default_rng(1)
+base1 = np.array(bench.GT, dtype=np.float64)
+A13 = np.stack([G.compose_index_matrix(g1, g1, G.params_to_matrix(base1 + rng.uniform(-0.5, 0.5, 6), (0.0, 0.0, 0.0))) for _ in range(13)])
+dA1 = torch.from_numpy(A13).to(dev)
+res["c1_ssd_i16_13_per_eval"] = timed(lambda: kernels.resample_ssd(f1, m1, d_A=dA1, mode="itk", ws=ws)) / 13
+res["path"] = _lib.load().mia_debug_last_path()
 del f1, m1
 
 # config 3 shape, float32, 13 device matrices per launch
