@@ -300,10 +300,10 @@ int try_tile_box(int mode, const void *d_mov, const int mdims[3], const double *
 // evaluation, 13 probes (int16 512x512x100 / float32 256^3): one matrix per CTA 66.8 / 43.7 us; G = 1: 76.7 / 47.7;
 // G = 2: 59.8 / 39.1; G = 3: 64.1 / 39.8 (25 warps put 7 on one scheduler: 72 registers, spills).
 #ifndef MIA_MULTI_I16
-#define MIA_MULTI_I16 4, 2
+#define MIA_MULTI_I16 3, 2
 #endif
 #ifndef MIA_MULTI_F32
-#define MIA_MULTI_F32 3, 2
+#define MIA_MULTI_F32 2, 2
 #endif
 template <int NST_, int G_> struct MultiCfgT { static constexpr int NST = NST_, G = G_; };
 template <typename TM> struct MultiCfg;
@@ -317,7 +317,7 @@ int launch_multi(const CUtensorMap &map, const KParams &p, int n_mats, cudaStrea
     constexpr int NST = MultiCfg<TM>::NST, G = MultiCfg<TM>::G;
     constexpr int threads = 32 * (kConsumerWarps * G + 1);
     auto k = tile_multi_kernel<TM, TM, VTK, BOX, NST, G>;
-    const size_t smem = MultiSmem<TM, BOX, NST>::kBytes;
+    const size_t smem = MultiSmem<TM, BOX, NST, G>::kBytes;
     static std::mutex mu;
     static std::map<int, int> occ;                         // device -> resident CTAs per SM
     int dev = 0;

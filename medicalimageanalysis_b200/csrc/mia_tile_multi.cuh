@@ -25,23 +25,23 @@ constexpr int kMaxMulti = 16;      // matrices per launch on this path (lane = m
 // cross-lane reduction sits between two tiles.
 constexpr int kMultiLanes = kConsumerWarps * 32;          // threads of one consumer group
 
-template <typename TM, class BOX, int NST>
+template <typename TM, class BOX, int NST, int G>
 struct MultiSmem {
     static constexpr unsigned kBoxBytes = BOX::kX * BOX::kY * BOX::kZ * sizeof(TM);
     static constexpr unsigned kStageBytes = (kBoxBytes + 127u) & ~127u;
     static constexpr unsigned kBarOff = kStageBytes * NST;
     static constexpr unsigned kInfoOff = kBarOff + 16u * NST;                                  // TileInfo[NST][kMaxMulti]
     static constexpr unsigned kMatOff = kInfoOff + (unsigned)sizeof(TileInfo) * NST * kMaxMulti;   // double[kMaxMulti][12]
-    static constexpr unsigned kAccOff = kMatOff + 8u * 12u * kMaxMulti;                        // double[kMaxMulti][256]
-    static constexpr unsigned kCntOff = kAccOff + 8u * kMaxMulti * kMultiLanes;                // unsigned[kMaxMulti][256]
-    static constexpr unsigned kBytes = kCntOff + 4u * kMaxMulti * kMultiLanes;
+    static constexpr unsigned kAccOff = kMatOff + 8u * 12u * kMaxMulti;                        // double[G][kMaxMulti][256]
+    static constexpr unsigned kCntOff = kAccOff + 8u * G * kMaxMulti * kMultiLanes;            // unsigned[G][kMaxMulti][256]
+    static constexpr unsigned kBytes = kCntOff + 4u * G * kMaxMulti * kMultiLanes;
 };
 
 template <typename TM, typename TF, bool VTK, class BOX, int NST, int G>
 __global__ void __launch_bounds__(32 * (kConsumerWarps * G + 1), 1)
 tile_multi_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ KParams p, const int n_mats)
 {
-    using L = MultiSmem<TM, BOX, NST>;
+    using L = MultiSmem<TM, BOX, NST, G>;
     extern __shared__ __align__(1024) unsigned char tsm[];
     __shared__ bool s_last;
 
@@ -55,7 +55,7 @@ tile_multi_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constan
     const uint32_t bar0 = smem_u32(tsm + L::kBarOff);       // full[s] = bar0 + 8 s, empty[s] = bar0 + 8 (NST + s)
 
     for (int q = tid; q < 12 * n_mats; q += kThreads) s_A[q] = p.dA[q];
-    for (int q = tid; q < kMaxMulti * kMultiLanes; q += kThreads) {
+    for (int q = tid; q < G * kMaxMulti * kMultiLanes; q += kThreads) {
         s_acc[q] = 0.0;
         s_cnt[q] = 0u;
     }
@@ -137,7 +137,10 @@ tile_multi_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constan
         }
     } else {
         // ---------------- consumers: G groups of 8 warps, every group against the same box ----------------
-        const int slot = warp * 32 + lane;
+        // accumulators are private to (group, matrix, thread): the groups drift apart by up to a ring stage and
+        // take turns on every matrix (see the loop below), so they must not share a slot
+        double *g_acc = s_acc + (size_t)grp * kMaxMulti * kMultiLanes + warp * 32 + lane;
+        unsigned *g_cnt = s_cnt + (size_t)grp * kMaxMulti * kMultiLanes + warp * 32 + lane;
         const unsigned plane = (unsigned)p.oy * (unsigned)p.ox;
         unsigned s = 0, ph = 0;
         for (int n = 0; n < ntile_mine; ++n) {
@@ -153,7 +156,9 @@ tile_multi_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constan
             }
             mbar_wait<32>(bar0 + 8 * s, ph);
             const unsigned char *stage = tsm + L::kStageBytes * s;
-            for (int m = grp; m < n_mats; m += G) {
+            // group (grp + n) mod G starts at matrix 0: with 13 matrices and 2 groups the 7 / 6 split alternates
+            // from tile to tile and both groups do the same work over two tiles
+            for (int m = (grp + n) % G; m < n_mats; m += G) {
                 const TileInfo ti = infos[s * kMaxMulti + m];
                 if (ti.cls == kOutside) continue;                    // warp-uniform
                 double acc = 0.0;
@@ -170,8 +175,8 @@ tile_multi_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constan
                                                                                        nullptr, fv, nullptr, 0);
                 }
                 // per-thread accumulators in shared memory: nothing between two tiles waits on another lane
-                s_acc[m * kMultiLanes + slot] += acc;
-                s_cnt[m * kMultiLanes + slot] += cnt;
+                g_acc[m * kMultiLanes] += acc;
+                g_cnt[m * kMultiLanes] += cnt;
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(bar0 + 8 * (NST + s));
@@ -185,10 +190,11 @@ tile_multi_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constan
     for (int m = wid; m < n_mats; m += kThreads / 32) {
         double sa = 0.0;
         unsigned c = 0;
-        for (int q = lane; q < kMultiLanes; q += 32) {
-            sa += s_acc[m * kMultiLanes + q];
-            c += s_cnt[m * kMultiLanes + q];
-        }
+        for (int g = 0; g < G; ++g)
+            for (int q = lane; q < kMultiLanes; q += 32) {
+                sa += s_acc[(g * kMaxMulti + m) * kMultiLanes + q];
+                c += s_cnt[(g * kMaxMulti + m) * kMultiLanes + q];
+            }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             sa += __shfl_xor_sync(0xffffffffu, sa, o);
