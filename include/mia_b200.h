@@ -138,6 +138,28 @@ int mia_optimizer_read(const void *d_state, double params[6], double *scale, int
                        int *n_reject, double *hist_cost, double *hist_params, double *hist_scale,
                        int max_hist, void *stream);
 
+/*
+ * SURVEY N1 -- displacement fields next to the rigid path.
+ *
+ * mia_warp_dvf replaces the second stage of Deformable.create_image (structure/deformable.py:797-806:
+ * sitk.Resample(image, sitk.DisplacementFieldTransform(dvf), sitk.sitkLinear, -3001, pixel id)).  d_dvf holds
+ * one physical displacement (x, y, z) per OUTPUT voxel, float32, reference layout [z][y][x][3] (self.dvf,
+ * deformable.py:797).  Output voxel idx is sampled at moving index  A . (idx, 1) + B . d :
+ * A = W2P_image . P2W_out (3x4, row-major), B = linear part of W2P_image (3x3, row-major).  Inside rule,
+ * rounding and background as mia_resample_rigid; the output keeps the image's pixel type.
+ */
+int mia_warp_dvf(const void *d_mov, int mov_dtype, const int mdims[3], const float *d_dvf, void *d_out, int out_dtype,
+                 const int odims[3], const double A[12], const double B[9], double background, int mode, void *stream);
+
+/*
+ * scipy.ndimage.map_coordinates(field[..., c], [z, y, x], order=1, mode='nearest') for a point set, all channels
+ * in one pass (structure/deformable.py:868-878 and :1095-1104: ROI mesh vertices through the DVF).
+ * d_field: float32 [z][y][x][channels]; d_pts: float64 [n][3] continuous voxel coordinates (x, y, z);
+ * d_out: float64 [n][channels] = scale * interpolated value (the reference's `percent / 100`).
+ */
+int mia_sample_field_points(const float *d_field, const int dims[3], int channels, const double *d_pts, long long n,
+                            double scale, double *d_out, void *stream);
+
 /* Page-locked host buffers for the *_host entry point (a NumPy array can wrap them). */
 void *mia_host_alloc(size_t bytes);
 int mia_host_free(void *p);

@@ -38,6 +38,8 @@ SIGNATURES = {
     "mia_optimizer_init": (_i, [_vp, _dp, _dp, _dp, _dp, _d, _d, _d, _i, _vp, _vp]),
     "mia_optimizer_step": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
     "mia_optimizer_read": (_i, [_vp, _dp, _dp, _ip, _ip, _ip, _dp, _dp, _dp, _i, _vp]),
+    "mia_warp_dvf": (_i, [_vp, _i, _ip, _vp, _vp, _i, _ip, _dp, _dp, _d, _i, _vp]),
+    "mia_sample_field_points": (_i, [_vp, _ip, _i, _vp, _c.c_longlong, _d, _vp, _vp]),
     "mia_host_alloc": (_vp, [_sz]),
     "mia_host_free": (_i, [_vp]),
 }

@@ -16,6 +16,7 @@
 #include "mia_optimizer.cuh"
 #include "mia_tile.cuh"
 #include "mia_tile_multi.cuh"
+#include "mia_dvf.cuh"
 
 using namespace mia;
 
@@ -569,3 +570,4 @@ int mia_mi_from_hist(const unsigned int *d_hist, int bins, int n_mats, double *d
 }  // extern "C"
 
 #include "mia_host_api.inl"
+#include "mia_dvf.inl"

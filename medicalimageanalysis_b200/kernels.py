@@ -194,6 +194,50 @@ def mi_from_hist(hist, out=None):
     return out
 
 
+def warp_dvf(mov, dvf, A, B, background=-3001.0, mode="itk", out=None):
+    """Sample ``mov`` at ``A . (idx, 1) + B . dvf[idx]`` for every voxel of the DVF lattice (second
+    stage of ``Deformable.create_image``).  ``dvf``: CUDA float32 ``[z, y, x, 3]`` physical displacements
+    (x, y, z); ``A``: 3x4 output index -> image index; ``B``: 3x3 physical -> image index (linear part)."""
+    lib = _lib.load()
+    mov = _vol(mov, "mov")
+    if not (isinstance(dvf, torch.Tensor) and dvf.is_cuda and dvf.dtype == torch.float32 and dvf.dim() == 4
+            and dvf.shape[3] == 3 and dvf.is_contiguous()):
+        raise TypeError("dvf must be a contiguous CUDA float32 tensor [z, y, x, 3]")
+    oshape = tuple(int(v) for v in dvf.shape[:3])
+    if out is None:
+        out = torch.empty(oshape, dtype=mov.dtype, device=mov.device)
+    else:
+        out = _vol(out, "out")
+    A = _mats(A)
+    B = np.ascontiguousarray(np.asarray(B, dtype=np.float64).reshape(3, 3))
+    with torch.cuda.device(mov.device):
+        check(lib.mia_warp_dvf(mov.data_ptr(), _DT[mov.dtype], _dims(mov), dvf.data_ptr(), out.data_ptr(),
+                               _DT[out.dtype], i3((oshape[2], oshape[1], oshape[0])), darr(A.ravel()), darr(B.ravel()),
+                               float(background), _MODE[mode], _stream(mov)))
+    return out
+
+
+def sample_field_points(field, points_xyz, scale=1.0, out=None):
+    """``scipy.ndimage.map_coordinates(field[..., c], [z, y, x], order=1, mode='nearest')`` for all channels.
+    ``field``: CUDA float32 ``[z, y, x, C]``; ``points_xyz``: CUDA float64 ``[n, 3]`` voxel coordinates (x, y, z).
+    Returns CUDA float64 ``[n, C]`` (times ``scale``)."""
+    lib = _lib.load()
+    if not (isinstance(field, torch.Tensor) and field.is_cuda and field.dtype == torch.float32 and field.dim() == 4
+            and field.is_contiguous()):
+        raise TypeError("field must be a contiguous CUDA float32 tensor [z, y, x, C]")
+    pts = points_xyz
+    if not (isinstance(pts, torch.Tensor) and pts.is_cuda and pts.dtype == torch.float64 and pts.dim() == 2
+            and pts.shape[1] == 3 and pts.is_contiguous()):
+        raise TypeError("points_xyz must be a contiguous CUDA float64 tensor [n, 3]")
+    n, C = int(pts.shape[0]), int(field.shape[3])
+    if out is None:
+        out = torch.empty((n, C), dtype=torch.float64, device=field.device)
+    with torch.cuda.device(field.device):
+        check(lib.mia_sample_field_points(field.data_ptr(), i3((field.shape[2], field.shape[1], field.shape[0])), C,
+                                          pts.data_ptr(), n, float(scale), out.data_ptr(), _stream(field)))
+    return out
+
+
 def autocrop_extent(M, p2w_mov, mdims, out_spacing, extent_rule="round"):
     """Host helper mirroring ``geometry.autocrop_extent`` through the C ABI."""
     lib = _lib.load()

@@ -1,4 +1,5 @@
 from . import rigid
+from . import deformable
 from .creation import CreateImageFromMask
 
-__all__ = ["rigid", "CreateImageFromMask"]
+__all__ = ["rigid", "deformable", "CreateImageFromMask"]

@@ -1,0 +1,112 @@
+"""Displacement-field kernels against the oracle and, for the point sampler, against
+``scipy.ndimage.map_coordinates`` itself (the reference's call, ``structure/deformable.py:873-878``)."""
+import numpy as np
+import pytest
+import torch
+from scipy import ndimage
+
+from medicalimageanalysis_b200 import Data, geometry as G, kernels
+from medicalimageanalysis_b200.phantom import make_phantom
+from medicalimageanalysis_b200.utils import CreateImageFromMask, deformable
+from oracle import dvf as D
+from tests.test_oracle_dvf import _smooth_field
+
+pytestmark = pytest.mark.gpu
+
+
+def _case(shape, sp, seed):
+    g = G.Grid((shape[2], shape[1], shape[0]), sp, tuple(-0.5 * np.array(sp) * np.array(shape[::-1])))
+    w2p = G.physical_to_index(g, "itk")
+    return g, (w2p @ G.index_to_physical(g, "itk"))[:3], w2p[:3, :3]
+
+
+@pytest.mark.parametrize("dtype", [np.int16, np.float32])
+@pytest.mark.parametrize("mode", ["itk", "vtk"])
+def test_warp_dvf_matches_oracle(cuda_device, dtype, mode):
+    shape, sp = (37, 45, 70), (1.0, 1.1, 2.0)
+    g, A, B = _case(shape, sp, 0)
+    img = make_phantom(shape, "CT", seed=4, spacing=sp).astype(dtype)
+    field = _smooth_field(shape, 4.0, 5)
+    field[:3] += 60.0                                   # pushes the first planes out of the volume: background
+    got = kernels.warp_dvf(torch.from_numpy(img).to(cuda_device), torch.from_numpy(field).to(cuda_device), A, B,
+                           background=-3001.0, mode=mode).cpu().numpy()
+    want = D.oracle_warp_dvf(img, field, A, B, background=-3001.0, mode=mode)
+    assert (want == -3001).mean() > 0.02
+    if dtype == np.int16:
+        d = np.abs(got.astype(np.int32) - want.astype(np.int32))
+        # float32 taps and weights against the float64 oracle: rounding ties only, and inside/outside flips on the
+        # half-voxel border where the float32 displacement meets a float64 coordinate
+        edge = (got == -3001) != (want == -3001)
+        assert edge.mean() < 1e-4
+        assert d[~edge].max() <= 1 and (d[~edge] > 0).mean() < 2e-3
+    else:
+        edge = (got == -3001) != (want == -3001)
+        assert edge.mean() < 1e-4
+        assert np.allclose(got[~edge], want[~edge], rtol=1e-4, atol=1e-2)
+
+
+def test_warp_zero_field_is_identity_and_constant_field_is_a_translation(cuda_device):
+    shape, sp = (24, 40, 64), (1.0, 1.0, 2.5)
+    g, A, B = _case(shape, sp, 0)
+    img = make_phantom(shape, "CT", seed=6, spacing=sp)
+    t = torch.from_numpy(img).to(cuda_device)
+    zero = torch.zeros(shape + (3,), dtype=torch.float32, device=cuda_device)
+    assert torch.equal(kernels.warp_dvf(t, zero, A, B, mode="itk"), t)
+    shift = np.array([2.0, -3.0, 5.0], dtype=np.float32)            # whole voxels: (2, -3, 2)
+    const = torch.from_numpy(np.broadcast_to(shift, shape + (3,)).copy()).to(cuda_device)
+    As = A.copy()
+    As[:, 3] += B @ shift.astype(np.float64)
+    assert torch.equal(kernels.warp_dvf(t, const, A, B, background=-3001.0, mode="itk"),
+                       kernels.resample(t, As, shape, background=-3001.0, mode="itk"))
+
+
+def test_point_sampler_equals_scipy_map_coordinates(cuda_device):
+    shape = (19, 23, 31)
+    field = _smooth_field(shape, 3.0, 7)
+    rng = np.random.default_rng(8)
+    pts = rng.uniform(-3.0, 34.0, (20000, 3))
+    pts[:100] = np.round(pts[:100])
+    got = kernels.sample_field_points(torch.from_numpy(field).to(cuda_device), torch.from_numpy(pts).to(cuda_device),
+                                      scale=0.6).cpu().numpy()
+    for c in range(3):
+        want = ndimage.map_coordinates(0.6 * field[..., c].astype(np.float64), [pts[:, 2], pts[:, 1], pts[:, 0]],
+                                       order=1, mode="nearest")
+        assert np.allclose(got[:, c], want, rtol=0, atol=1e-12)
+    assert np.allclose(got, D.oracle_sample_field_points(field, pts, 0.6), rtol=0, atol=1e-12)
+    empty = kernels.sample_field_points(torch.from_numpy(field).to(cuda_device),
+                                        torch.zeros((0, 3), dtype=torch.float64, device=cuda_device))
+    assert tuple(empty.shape) == (0, 3)
+
+
+def test_deformable_operators_follow_the_reference_recipe(cuda_device):
+    """``utils.deformable``: displace_points == the reference's map_coordinates loop; resample_and_warp == rigid ITK
+    resample followed by the field resample, both checked against the oracle composition."""
+    from medicalimageanalysis_b200.utils import rigid as R
+    from oracle import reslice
+    shape, sp = (24, 36, 48), (1.2, 1.2, 2.0)
+    origin = (-28.0, -21.0, -24.0)
+    Data.clear()
+    ref = make_phantom(shape, "CT", seed=9, spacing=sp)
+    M = G.params_to_matrix([2.0, -1.0, 3.0, 2.0, 1.0, -2.0], (0, 0, 0))
+    mov = make_phantom(shape, "CT", seed=9, spacing=sp, world_matrix=np.linalg.inv(M))
+    f = CreateImageFromMask(ref, origin, sp, "ref", device=cuda_device).add_image()
+    m = CreateImageFromMask(mov, origin, sp, "mov", device=cuda_device).add_image()
+    field = _smooth_field(shape, 2.5, 10)
+    got = deformable.resample_and_warp(m, f, M, field).cpu().numpy()
+    A1 = G.compose_index_matrix(f.grid, m.grid, M, convention="itk")
+    stage = reslice.oracle_reslice(mov, A1, f.grid.dims, background=-3001.0, mode="itk")
+    w2p = G.physical_to_index(f.grid, "itk")
+    want = D.oracle_warp_dvf(stage, field, (w2p @ G.index_to_physical(f.grid, "itk"))[:3], w2p[:3, :3], mode="itk")
+    d = np.abs(got.astype(np.int32) - want.astype(np.int32))
+    edge = (got == -3001) != (want == -3001)
+    assert edge.mean() < 2e-3 and (d[~edge] > 1).mean() < 2e-3      # stage-1 rounding ties propagate through stage 2
+    rng = np.random.default_rng(12)
+    pts = rng.uniform(-30, 30, (5000, 3))
+    moved = deformable.displace_points(pts, field, origin, sp, percent=40.0)
+    vox = (pts - np.asarray(origin)) / np.asarray(sp)
+    want_pts = pts.copy()
+    for i in range(3):
+        want_pts[:, i] += ndimage.map_coordinates((40.0 * field[..., i].astype(np.float64)) / 100,
+                                                  [vox[:, 2], vox[:, 1], vox[:, 0]], order=1, mode="nearest")
+    assert np.allclose(moved, want_pts, rtol=0, atol=1e-11)
+    Data.clear()
