@@ -72,14 +72,13 @@ __device__ __forceinline__ RowCtx make_row_ctx(const double *__restrict__ A, int
     return r;
 }
 
-// Sample voxel number v (0..V-1) of the thread.  Returns inside flag; value in `val` (unrounded float32).
+// Trilinear sample at LOCAL coordinates (lx, ly, lz) relative to the integer base of `r`.  Returns the inside
+// flag; value in `val` (unrounded float32).  When all 8 taps lie inside the volume (the common case) they are
+// addressed from one base pointer; otherwise neighbour indices are clamped to the buffer.
 template <typename TM, bool CLOSED>
-__device__ __forceinline__ bool sample_voxel(const TM *__restrict__ mov, int nx, int ny, int nz,
-                                             const RowCtx &r, int v, float &val)
+__device__ __forceinline__ bool sample_local(const TM *__restrict__ mov, int nx, int ny, int nz, const RowCtx &r,
+                                             float lx, float ly, float lz, float &val)
 {
-    const float lx = fmaf((float)v, r.ax, r.fx);
-    const float ly = fmaf((float)v, r.ay, r.fy);
-    const float lz = fmaf((float)v, r.az, r.fz);
     bool in = (lx >= r.lox) & (ly >= r.loy) & (lz >= r.loz);
     if (CLOSED)
         in &= (lx <= r.hix) & (ly <= r.hiy) & (lz <= r.hiz);
@@ -89,15 +88,25 @@ __device__ __forceinline__ bool sample_voxel(const TM *__restrict__ mov, int nx,
     const float flx = floorf(lx), fly = floorf(ly), flz = floorf(lz);
     const float wx = lx - flx, wy = ly - fly, wz = lz - flz;
     const int ix = r.bx + (int)flx, iy = r.by + (int)fly, iz = r.bz + (int)flz;
-    const int x0 = clampi(ix, 0, nx - 1), x1 = clampi(ix + 1, 0, nx - 1);
-    const int y0 = clampi(iy, 0, ny - 1), y1 = clampi(iy + 1, 0, ny - 1);
-    const int z0 = clampi(iz, 0, nz - 1), z1 = clampi(iz + 1, 0, nz - 1);
-    const size_t r00 = ((size_t)z0 * ny + y0) * nx, r10 = ((size_t)z0 * ny + y1) * nx;
-    const size_t r01 = ((size_t)z1 * ny + y0) * nx, r11 = ((size_t)z1 * ny + y1) * nx;
-    const float v000 = ld_tap(mov, r00 + x0), v100 = ld_tap(mov, r00 + x1);
-    const float v010 = ld_tap(mov, r10 + x0), v110 = ld_tap(mov, r10 + x1);
-    const float v001 = ld_tap(mov, r01 + x0), v101 = ld_tap(mov, r01 + x1);
-    const float v011 = ld_tap(mov, r11 + x0), v111 = ld_tap(mov, r11 + x1);
+    float v000, v100, v010, v110, v001, v101, v011, v111;
+    if (((unsigned)ix < (unsigned)(nx - 1)) & ((unsigned)iy < (unsigned)(ny - 1)) & ((unsigned)iz < (unsigned)(nz - 1))) {
+        const TM *__restrict__ q = mov + (((size_t)iz * ny + iy) * nx + ix);
+        const size_t py = (size_t)nx, pz = (size_t)nx * ny;
+        v000 = (float)__ldg(q); v100 = (float)__ldg(q + 1);
+        v010 = (float)__ldg(q + py); v110 = (float)__ldg(q + py + 1);
+        v001 = (float)__ldg(q + pz); v101 = (float)__ldg(q + pz + 1);
+        v011 = (float)__ldg(q + pz + py); v111 = (float)__ldg(q + pz + py + 1);
+    } else {
+        const int x0 = clampi(ix, 0, nx - 1), x1 = clampi(ix + 1, 0, nx - 1);
+        const int y0 = clampi(iy, 0, ny - 1), y1 = clampi(iy + 1, 0, ny - 1);
+        const int z0 = clampi(iz, 0, nz - 1), z1 = clampi(iz + 1, 0, nz - 1);
+        const size_t r00 = ((size_t)z0 * ny + y0) * nx, r10 = ((size_t)z0 * ny + y1) * nx;
+        const size_t r01 = ((size_t)z1 * ny + y0) * nx, r11 = ((size_t)z1 * ny + y1) * nx;
+        v000 = ld_tap(mov, r00 + x0); v100 = ld_tap(mov, r00 + x1);
+        v010 = ld_tap(mov, r10 + x0); v110 = ld_tap(mov, r10 + x1);
+        v001 = ld_tap(mov, r01 + x0); v101 = ld_tap(mov, r01 + x1);
+        v011 = ld_tap(mov, r11 + x0); v111 = ld_tap(mov, r11 + x1);
+    }
     const float vx00 = fmaf(wx, v100 - v000, v000);
     const float vx10 = fmaf(wx, v110 - v010, v010);
     const float vx01 = fmaf(wx, v101 - v001, v001);
@@ -106,6 +115,15 @@ __device__ __forceinline__ bool sample_voxel(const TM *__restrict__ mov, int nx,
     const float vxx1 = fmaf(wy, vx11 - vx01, vx01);
     val = fmaf(wz, vxx1 - vxx0, vxx0);
     return true;
+}
+
+// Sample voxel number v (0..V-1) of the thread.  Returns inside flag; value in `val` (unrounded float32).
+template <typename TM, bool CLOSED>
+__device__ __forceinline__ bool sample_voxel(const TM *__restrict__ mov, int nx, int ny, int nz,
+                                             const RowCtx &r, int v, float &val)
+{
+    return sample_local<TM, CLOSED>(mov, nx, ny, nz, r, fmaf((float)v, r.ax, r.fx), fmaf((float)v, r.ay, r.fy),
+                                    fmaf((float)v, r.az, r.fz), val);
 }
 
 // float -> output element.  ROUND: 0 = floor(v + 0.5) (VTK), 1 = trunc (ITK); clamp to the type range first.

@@ -47,35 +47,63 @@ __device__ __forceinline__ RowCtx make_point_ctx(double cx, double cy, double cz
 }
 
 constexpr int kDvfThreads = 256;
+#ifndef MIA_DVF_TZ
+#define MIA_DVF_TZ 8
+#endif
+#ifndef MIA_DVF_MINB
+#define MIA_DVF_MINB 2
+#endif
+constexpr int kDvfTZ = MIA_DVF_TZ;   // planes per thread: the float64 part of the coordinate is paid once per kDvfTZ voxels
 
+// Work item = 32 (x) x 8 (y) x 8 (z) output voxels per CTA pass: lane = x (coalesced field reads and stores),
+// warp = y row, each thread walks 8 z planes.  The rigid part of the coordinate is mapped in float64 once per
+// thread and split into an integer base and a float32 fraction; the plane step and the displacement B . d are
+// added in float32 LOCAL coordinates (|l| of a few voxels), so the weights stay exact to ~1e-7 voxel.
 template <typename TM, typename TO, bool CLOSED>
-__global__ void __launch_bounds__(kDvfThreads) warp_dvf_kernel(const DvfParams p)
+__global__ void __launch_bounds__(kDvfThreads, MIA_DVF_MINB) warp_dvf_kernel(const DvfParams p)
 {
     const TM *__restrict__ mov = static_cast<const TM *>(p.mov.p);
     TO *__restrict__ out = static_cast<TO *>(p.out);
-    const long long rows = (long long)p.oy * p.oz;
-    const int xchunks = (p.ox + kDvfThreads - 1) / kDvfThreads;
-    const long long nwork = rows * xchunks;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ntx = (p.ox + 31) / 32, nty = (p.oy + 7) / 8, ntz = (p.oz + kDvfTZ - 1) / kDvfTZ;
+    const long long ntiles = (long long)ntx * nty * ntz;
     const TO bg = to_out<TO>(p.background, p.round_mode);
-    for (long long w = blockIdx.x; w < nwork; w += gridDim.x) {
-        const long long row = w / xchunks;
-        const int i = (int)(w % xchunks) * kDvfThreads + threadIdx.x;
-        if (i >= p.ox) continue;
-        const int j = (int)(row % p.oy), k = (int)(row / p.oy);
-        const size_t v = (size_t)row * p.ox + i;
-        const float dx = __ldg(p.dvf + 3 * v), dy = __ldg(p.dvf + 3 * v + 1), dz = __ldg(p.dvf + 3 * v + 2);
-        const double *A = p.A.a;
-        // origin + k*z + j*y + i*x as in make_row_ctx, then the displacement
-        const double cx = (((A[3] + (double)k * A[2]) + (double)j * A[1]) + (double)i * A[0]) +
-                          ((p.B[0] * (double)dx + p.B[1] * (double)dy) + p.B[2] * (double)dz);
-        const double cy = (((A[7] + (double)k * A[6]) + (double)j * A[5]) + (double)i * A[4]) +
-                          ((p.B[3] * (double)dx + p.B[4] * (double)dy) + p.B[5] * (double)dz);
-        const double cz = (((A[11] + (double)k * A[10]) + (double)j * A[9]) + (double)i * A[8]) +
-                          ((p.B[6] * (double)dx + p.B[7] * (double)dy) + p.B[8] * (double)dz);
+    const double *A = p.A.a;
+    const float a2x = (float)A[2], a2y = (float)A[6], a2z = (float)A[10];
+    const float b00 = (float)p.B[0], b01 = (float)p.B[1], b02 = (float)p.B[2];
+    const float b10 = (float)p.B[3], b11 = (float)p.B[4], b12 = (float)p.B[5];
+    const float b20 = (float)p.B[6], b21 = (float)p.B[7], b22 = (float)p.B[8];
+    const size_t plane = (size_t)p.oy * p.ox;
+    for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const int tz = (int)(t / ((long long)ntx * nty)), r2 = (int)(t % ((long long)ntx * nty));
+        const int i = (r2 % ntx) * 32 + lane, j = (r2 / ntx) * 8 + warp, k0 = tz * kDvfTZ;
+        if (i >= p.ox || j >= p.oy) continue;
+        const int kcnt = min(kDvfTZ, p.oz - k0);
+        const double cx = ((A[3] + (double)k0 * A[2]) + (double)j * A[1]) + (double)i * A[0];
+        const double cy = ((A[7] + (double)k0 * A[6]) + (double)j * A[5]) + (double)i * A[4];
+        const double cz = ((A[11] + (double)k0 * A[10]) + (double)j * A[9]) + (double)i * A[8];
         const RowCtx r = make_point_ctx(cx, cy, cz, p.mov.nx, p.mov.ny, p.mov.nz);
-        float val = 0.0f;
-        const bool in = sample_voxel<TM, CLOSED>(mov, p.mov.nx, p.mov.ny, p.mov.nz, r, 0, val);
-        out[v] = in ? to_out<TO>(val, p.round_mode) : bg;
+        size_t v = ((size_t)k0 * p.oy + j) * p.ox + i;
+        float d[kDvfTZ][3];
+#pragma unroll
+        for (int kz = 0; kz < kDvfTZ; ++kz) {          // all field loads of the thread in flight before the gathers
+            const bool live = kz < kcnt;
+            const float *q = p.dvf + 3 * (v + (size_t)kz * plane);
+            d[kz][0] = live ? __ldg(q) : 0.0f;
+            d[kz][1] = live ? __ldg(q + 1) : 0.0f;
+            d[kz][2] = live ? __ldg(q + 2) : 0.0f;
+        }
+#pragma unroll
+        for (int kz = 0; kz < kDvfTZ; ++kz) {
+            if (kz < kcnt) {
+                const float lx = fmaf((float)kz, a2x, r.fx) + fmaf(b02, d[kz][2], fmaf(b01, d[kz][1], b00 * d[kz][0]));
+                const float ly = fmaf((float)kz, a2y, r.fy) + fmaf(b12, d[kz][2], fmaf(b11, d[kz][1], b10 * d[kz][0]));
+                const float lz = fmaf((float)kz, a2z, r.fz) + fmaf(b22, d[kz][2], fmaf(b21, d[kz][1], b20 * d[kz][0]));
+                float val = 0.0f;
+                const bool in = sample_local<TM, CLOSED>(mov, p.mov.nx, p.mov.ny, p.mov.nz, r, lx, ly, lz, val);
+                out[v + (size_t)kz * plane] = in ? to_out<TO>(val, p.round_mode) : bg;
+            }
+        }
     }
 }
 

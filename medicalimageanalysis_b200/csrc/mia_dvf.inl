@@ -36,7 +36,7 @@ int mia_warp_dvf(const void *d_mov, int mov_dtype, const int mdims[3], const flo
     memcpy(p.B, B, sizeof(double) * 9);
     p.background = (float)background;
     p.round_mode = mode == MIA_MODE_VTK ? 0 : 1;
-    const long long nwork = (long long)odims[1] * odims[2] * ((odims[0] + mia::kDvfThreads - 1) / mia::kDvfThreads);
+    const long long nwork = (long long)((odims[0] + 31) / 32) * ((odims[1] + 7) / 8) * ((odims[2] + mia::kDvfTZ - 1) / mia::kDvfTZ);
     long long gx = (long long)sm_count() * 8;
     if (gx > nwork) gx = nwork;
     cudaStream_t s = (cudaStream_t)stream;
