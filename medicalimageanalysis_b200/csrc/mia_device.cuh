@@ -31,10 +31,20 @@ struct Mat34 {
     double a[12];
 };
 
+// Global tap -> float32 through the read-only path.  int16 is loaded sign-extended into a 32-bit register so that
+// the conversion is the half-rate ALU I2FP.F32.S32 and not the quarter-rate XU I2F.S16 a C++ short load compiles to.
+__device__ __forceinline__ float ldg_f32(const float *p) { return __ldg(p); }
+__device__ __forceinline__ float ldg_f32(const int16_t *p)
+{
+    int v;
+    asm("ld.global.nc.s16 %0, [%1];" : "=r"(v) : "l"(p));
+    return (float)v;
+}
+
 template <typename T>
 __device__ __forceinline__ float ld_tap(const T *__restrict__ p, size_t i)
 {
-    return static_cast<float>(__ldg(p + i));
+    return ldg_f32(p + i);
 }
 
 __device__ __forceinline__ int clampi(int v, int lo, int hi) { return min(max(v, lo), hi); }
@@ -92,10 +102,10 @@ __device__ __forceinline__ bool sample_local(const TM *__restrict__ mov, int nx,
     if (((unsigned)ix < (unsigned)(nx - 1)) & ((unsigned)iy < (unsigned)(ny - 1)) & ((unsigned)iz < (unsigned)(nz - 1))) {
         const TM *__restrict__ q = mov + (((size_t)iz * ny + iy) * nx + ix);
         const size_t py = (size_t)nx, pz = (size_t)nx * ny;
-        v000 = (float)__ldg(q); v100 = (float)__ldg(q + 1);
-        v010 = (float)__ldg(q + py); v110 = (float)__ldg(q + py + 1);
-        v001 = (float)__ldg(q + pz); v101 = (float)__ldg(q + pz + 1);
-        v011 = (float)__ldg(q + pz + py); v111 = (float)__ldg(q + pz + py + 1);
+        v000 = ldg_f32(q); v100 = ldg_f32(q + 1);
+        v010 = ldg_f32(q + py); v110 = ldg_f32(q + py + 1);
+        v001 = ldg_f32(q + pz); v101 = ldg_f32(q + pz + 1);
+        v011 = ldg_f32(q + pz + py); v111 = ldg_f32(q + pz + py + 1);
     } else {
         const int x0 = clampi(ix, 0, nx - 1), x1 = clampi(ix + 1, 0, nx - 1);
         const int y0 = clampi(iy, 0, ny - 1), y1 = clampi(iy + 1, 0, ny - 1);

@@ -48,10 +48,10 @@ __device__ __forceinline__ RowCtx make_point_ctx(double cx, double cy, double cz
 
 constexpr int kDvfThreads = 256;
 #ifndef MIA_DVF_TZ
-#define MIA_DVF_TZ 8
+#define MIA_DVF_TZ 4
 #endif
 #ifndef MIA_DVF_MINB
-#define MIA_DVF_MINB 2
+#define MIA_DVF_MINB 4
 #endif
 constexpr int kDvfTZ = MIA_DVF_TZ;   // planes per thread: the float64 part of the coordinate is paid once per kDvfTZ voxels
 
