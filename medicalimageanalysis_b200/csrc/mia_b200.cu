@@ -250,6 +250,7 @@ int launch_tile(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream
     const size_t smem = TileSmem<TM, BOX, NST>::bytes(METRIC == kHist ? p.bins : 0);
     static std::mutex mu;
     static std::map<std::pair<int, size_t>, int> occ;     // (device, smem) -> resident CTAs per SM
+    static std::map<int, size_t> attr;                    // device -> dynamic shared memory the kernel is allowed
     int dev = 0;
     CUDA_TRY(cudaGetDevice(&dev));
     int nb = 0;
@@ -257,7 +258,12 @@ int launch_tile(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream
         std::lock_guard<std::mutex> lock(mu);
         auto it = occ.find({dev, smem});
         if (it == occ.end()) {
-            CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            // only ever raise the limit: the histogram kernels come with several sizes (bins), and lowering it for a
+            // small one would make the next cached large launch fail
+            if (smem > attr[dev]) {
+                CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                attr[dev] = smem;
+            }
             CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k, kTileThreads, smem));
             if (nb < 1) return fail(MIA_ERR_UNSUPPORTED, "tile kernel does not fit on this device (%zu B smem)", smem);
             occ[{dev, smem}] = nb;
@@ -300,6 +306,9 @@ int try_tile_box(int mode, const void *d_mov, const int mdims[3], const double *
 // with G consumer groups.  (ring depth, groups) per element type; tuning builds override with -D.  Measured per
 // evaluation, 13 probes (int16 512x512x100 / float32 256^3): one matrix per CTA 66.8 / 43.7 us; G = 1: 76.7 / 47.7;
 // G = 2: 59.8 / 39.1; G = 3: 64.1 / 39.8 (25 warps put 7 on one scheduler: 72 registers, spills).
+// Tried and dropped: the same kernel with 8 privatised joint histograms per CTA (13 probes = launches of 8 + 5):
+// 55 us per evaluation against 48 for one matrix per CTA with the fixed image prefetched; and prefetching the next
+// tile position's fixed values here (39.0 against 38.1 us).
 #ifndef MIA_MULTI_I16
 #define MIA_MULTI_I16 3, 2
 #endif

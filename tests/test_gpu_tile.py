@@ -227,3 +227,22 @@ def test_multi_matrix_handles_outside_and_ragged(cuda_device):
             want, n = native.reslice_ssd(fixed, mov, A[i], "itk")
             assert abs(int(c[i]) - n) <= 2
             assert abs(float(s[i]) - want) <= 1e-5 * max(want, 1.0)
+
+
+def test_histogram_sizes_in_any_order(cuda_device):
+    """The dynamic shared-memory limit of the histogram kernels is only ever raised: a small launch between two
+    large ones must not break the cached configuration of the large one (regression)."""
+    shape, sp = (24, 40, 64), (1.0, 1.0, 2.0)
+    g = grid_of(shape, sp)
+    fixed = make_phantom(shape, "CT", seed=2, spacing=sp)
+    moving = make_phantom(shape, "CT", seed=3, spacing=sp)
+    f, m = torch.from_numpy(fixed).to(cuda_device), torch.from_numpy(moving).to(cuda_device)
+    A = G.compose_index_matrix(g, g, G.params_to_matrix([1, -1, 2, 1, 0, -1], (0, 0, 0)))
+    fr = (-1024.0, 3071.0)
+    ref = {}
+    for bins in (128, 16, 128, 64, 16, 128):
+        h, c = kernels.resample_jointhist(f, m, fr, fr, bins=bins, A=A, ws=kernels.MetricWorkspace(cuda_device, 1, bins))
+        assert last_path() == TILE and int(h.sum()) == int(c[0])
+        if bins in ref:
+            assert torch.equal(h, ref[bins])
+        ref[bins] = h.clone()
