@@ -117,9 +117,21 @@ int mia_permute_axes(const void *d_in, int dtype, const int idims[3], void *d_ou
         const bool vec = dtype == MIA_I16 && p.idim[2] % 2 == 0 && p.idim[perm[2]] % 2 == 0 &&
                          (((uintptr_t)d_in | (uintptr_t)d_out) & 3u) == 0;
         if (vec) {
+            // persistent blocks, DEPTH tiles of loads in flight per block (measured choice; env overrides for tuning)
             const long long vt = (long long)((p.idim[2] + 63) / 64) * ((p.idim[perm[2]] + 63) / 64) * p.odim[pc];
-            const long long vg = vt < 0x7fffffffLL ? vt : 0x7fffffffLL;       // one tile per block
-            permute_transpose_vec_i16_kernel<<<(unsigned)vg, 256, 0, s>>>(p, pa, pc);
+            static const int depth = [] { const char *e = getenv("MIA_TR_DEPTH"); return e ? atoi(e) : 2; }();
+            static const int bps = [] { const char *e = getenv("MIA_TR_BLOCKS"); return e ? atoi(e) : 4; }();
+            long long vg = (long long)sms * (bps > 0 ? bps : 4);
+            if (vg > vt) vg = vt;
+            const int nqd = p.idim[perm[2]];
+            const bool v16 = p.idim[2] % 8 == 0 && nqd % 4 == 0 && vt < 0x7fffffffLL &&
+                             (((uintptr_t)d_in | (uintptr_t)d_out) & 15u) == 0;
+            const bool w16 = nqd % 8 == 0;
+            if (!v16) permute_transpose_vec_i16_kernel<1><<<(unsigned)vg, 256, 0, s>>>(p, pa, pc);
+            else if (!w16) permute_transpose_v16_i16_kernel<2, false><<<(unsigned)vg, 256, 0, s>>>(p, pa, pc);
+            else if (depth == 1) permute_transpose_v16_i16_kernel<1, true><<<(unsigned)vg, 256, 0, s>>>(p, pa, pc);
+            else if (depth == 3) permute_transpose_v16_i16_kernel<3, true><<<(unsigned)vg, 256, 0, s>>>(p, pa, pc);
+            else permute_transpose_v16_i16_kernel<2, true><<<(unsigned)vg, 256, 0, s>>>(p, pa, pc);
         } else if (dtype == MIA_I16) permute_transpose_kernel<int16_t><<<(unsigned)g, block, 0, s>>>(p, pa, pc);
         else permute_transpose_kernel<float><<<(unsigned)g, block, 0, s>>>(p, pa, pc);
     }

@@ -367,7 +367,14 @@ __global__ void __launch_bounds__(256) permute_rows_vec_i16_kernel(const PermPar
 // Path B (input x becomes output axis pa): 64 x 64 tile, 2x2 register transposes so that both the global
 // loads (along input x) and the global stores (along input q = output x) are 4-byte, 128 B per warp.
 // Needs even idim[2] and even idim[q].
-__global__ void __launch_bounds__(256) permute_transpose_vec_i16_kernel(const PermParams p, int pa, int pc)
+//
+// Persistent and software-pipelined: a block walks tiles blockIdx.x + n * gridDim.x and keeps DEPTH tiles of
+// loads in flight in registers (8 words per thread and tile) while it transposes and stores the oldest one.
+// The one-tile-per-block first cut was latency-bound at 42 % of the HBM roofline: a block held 8 KB of loads
+// in flight only until they landed and then spent the rest of its life on shared memory, stores and the block
+// relaunch, so an SM averaged ~30 KB of reads in flight where Little's law asks for ~45 KB at 6.5 TB/s.
+template <int DEPTH>
+__global__ void __launch_bounds__(256, (DEPTH <= 1 ? 8 : (DEPTH <= 3 ? 4 : 3))) permute_transpose_vec_i16_kernel(const PermParams p, int pa, int pc)
 {
     __shared__ unsigned te[32][33], to[32][33];      // even / odd input x; [x / 2][q / 2]
     const int q = p.perm[2], c_in = p.perm[pc];
@@ -380,19 +387,27 @@ __global__ void __launch_bounds__(256) permute_transpose_vec_i16_kernel(const Pe
     const size_t ostr[3] = {(size_t)p.odim[1] * p.odim[2], (size_t)p.odim[2], 1};
     const unsigned sq = (unsigned)istr[q];             // input stride of the axis that becomes output x
     const unsigned sa = (unsigned)ostr[pa];            // output stride of the axis fed by input x
-    for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
-        const int tx0 = (int)(t % tiles_x) * 64;
+    const size_t sc_in = istr[c_in], sc_out = ostr[pc];
+    const bool fa = p.flip[pa] != 0, f2 = p.flip[2] != 0, fc = p.flip[pc] != 0;
+    const int nc = p.odim[pc];
+    const long long G = gridDim.x;
+
+    struct Loc { int tx0, tq0, oc; };
+    auto locate = [&](long long t) {
+        Loc l;
+        l.tx0 = (int)(t % tiles_x) * 64;
         const long long t2 = t / tiles_x;
-        const int tq0 = (int)(t2 % tiles_q) * 64;
-        const int oc = (int)(t2 / tiles_q);
-        const int ic = p.flip[pc] ? p.odim[pc] - 1 - oc : oc;
-        // tile bases (64-bit once per tile); everything inside the tile is a 32-bit offset
-        const int16_t *ibase = static_cast<const int16_t *>(p.in) + (size_t)ic * istr[c_in] + (size_t)tq0 * sq + tx0;
-        const int xo0 = p.flip[pa] ? nxin - 1 - tx0 : tx0;          // output index along pa of tile row 0
-        const int qo0 = p.flip[2] ? nq - 2 - tq0 : tq0;             // output x of the tile's first pair
-        int16_t *obase = static_cast<int16_t *>(p.out) + (size_t)oc * ostr[pc] + (size_t)xo0 * sa + qo0;
-        const int nxt = min(64, nxin - tx0), nqt = min(64, nq - tq0);
-        unsigned w0[4], w1[4];
+        l.tq0 = (int)(t2 % tiles_q) * 64;
+        l.oc = (int)(t2 / tiles_q);
+        return l;
+    };
+    auto load = [&](long long t, unsigned (&w0)[4], unsigned (&w1)[4]) {
+        if (t >= ntiles) return;
+        const Loc l = locate(t);
+        const int ic = fc ? nc - 1 - l.oc : l.oc;
+        // tile base (64-bit once per tile); everything inside the tile is a 32-bit offset
+        const int16_t *ibase = static_cast<const int16_t *>(p.in) + (size_t)ic * sc_in + (size_t)l.tq0 * sq + l.tx0;
+        const int nxt = min(64, nxin - l.tx0), nqt = min(64, nq - l.tq0);
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
             const int rr = warp + 8 * it;
@@ -403,28 +418,143 @@ __global__ void __launch_bounds__(256) permute_transpose_vec_i16_kernel(const Pe
                 w1[it] = __ldg(reinterpret_cast<const unsigned *>(ibase + e + sq));
             }
         }
+    };
+    unsigned w0[DEPTH][4], w1[DEPTH][4];
 #pragma unroll
-        for (int it = 0; it < 4; ++it) {
-            const int rr = warp + 8 * it;
-            te[lane][rr] = __byte_perm(w0[it], w1[it], 0x5410);      // (a[q][x],   a[q+1][x])
-            to[lane][rr] = __byte_perm(w0[it], w1[it], 0x7632);      // (a[q][x+1], a[q+1][x+1])
-        }
-        __syncthreads();
+    for (int d = 0; d < DEPTH; ++d) load((long long)blockIdx.x + d * G, w0[d], w1[d]);
+
+    for (long long tb = blockIdx.x; tb < ntiles; tb += DEPTH * G) {
 #pragma unroll
-        for (int it = 0; it < 8; ++it) {
-            const int xr = warp + 8 * it;
-            if (xr < nxt && 2 * lane < nqt) {
-                unsigned w = (xr & 1) ? to[xr >> 1][lane] : te[xr >> 1][lane];
-                const long long row = p.flip[pa] ? -(long long)xr * sa : (long long)xr * sa;
-                long long col = 2 * lane;
-                if (p.flip[2]) {
-                    col = -col;
-                    w = swap_halves(w);
-                }
-                *reinterpret_cast<unsigned *>(obase + row + col) = w;
+        for (int d = 0; d < DEPTH; ++d) {
+            const long long t = tb + d * G;
+            if (t >= ntiles) break;
+#pragma unroll
+            for (int it = 0; it < 4; ++it) {
+                const int rr = warp + 8 * it;
+                te[lane][rr] = __byte_perm(w0[d][it], w1[d][it], 0x5410);      // (a[q][x],   a[q+1][x])
+                to[lane][rr] = __byte_perm(w0[d][it], w1[d][it], 0x7632);      // (a[q][x+1], a[q+1][x+1])
             }
+            load(t + DEPTH * G, w0[d], w1[d]);        // the registers are free again: refill them DEPTH tiles ahead
+            __syncthreads();
+            const Loc l = locate(t);
+            const int xo0 = fa ? nxin - 1 - l.tx0 : l.tx0;          // output index along pa of tile row 0
+            const int qo0 = f2 ? nq - 2 - l.tq0 : l.tq0;             // output x of the tile's first pair
+            int16_t *obase = static_cast<int16_t *>(p.out) + (size_t)l.oc * sc_out + (size_t)xo0 * sa + qo0;
+            const int nxt = min(64, nxin - l.tx0), nqt = min(64, nq - l.tq0);
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+                const int xr = warp + 8 * it;
+                if (xr < nxt && 2 * lane < nqt) {
+                    unsigned w = (xr & 1) ? to[xr >> 1][lane] : te[xr >> 1][lane];
+                    const long long row = fa ? -(long long)xr * sa : (long long)xr * sa;
+                    long long col = 2 * lane;
+                    if (f2) {
+                        col = -col;
+                        w = swap_halves(w);
+                    }
+                    *reinterpret_cast<unsigned *>(obase + row + col) = w;
+                }
+            }
+            __syncthreads();
         }
-        __syncthreads();
+    }
+}
+
+// Path B, 16-byte version (needs idim[2] % 8 == 0, idim[q] % 8 == 0, 16-byte aligned bases): the 4-byte kernel above
+// is ISSUE-bound, not memory-bound (ncu: 83 % issue slots, 37 % DRAM, 36 lane-instructions per voxel -- 64-bit tile
+// arithmetic and one memory instruction per 2 voxels).  Here a thread moves 16 voxels per tile with 2 LDG.128,
+// 8 PRMT (2x2 transposes), 8 STS.32, 2 LDS.128 and 2 STG.128, and all tile arithmetic is 32-bit.
+// Shared tile T[x][q / 2] (64 rows of 32 words, no padding) with the 4-word column group XOR-swizzled by x / 8:
+// the writes of a warp (8 x-chunks x 4 row pairs) and the LDS.128 of a quarter warp (8 groups of one row) both
+// touch 32 different banks.
+// W16: output rows are 16-byte aligned (idim[q] % 8 == 0); otherwise idim[q] % 4 == 0 and the 8 voxels of a thread
+// leave as two 8-byte stores (the last group of a row may hold only 4).
+template <int DEPTH, bool W16>
+__global__ void __launch_bounds__(256) permute_transpose_v16_i16_kernel(const PermParams p, int pa, int pc)
+{
+    __shared__ __align__(16) unsigned T[64 * 32];
+    const int q = p.perm[2], c_in = p.perm[pc];
+    const int nxin = p.idim[2], nq = p.idim[q];
+    const unsigned tiles_x = (unsigned)(nxin + 63) / 64u, tiles_q = (unsigned)(nq + 63) / 64u;
+    const unsigned ntiles = tiles_x * tiles_q * (unsigned)p.odim[pc];
+    const size_t istr[3] = {(size_t)p.idim[1] * p.idim[2], (size_t)p.idim[2], 1};
+    const size_t ostr[3] = {(size_t)p.odim[1] * p.odim[2], (size_t)p.odim[2], 1};
+    const size_t sq = istr[q], sa = ostr[pa], sc_in = istr[c_in], sc_out = ostr[pc];
+    const bool fa = p.flip[pa] != 0, f2 = p.flip[2] != 0, fc = p.flip[pc] != 0;
+    const int nc = p.odim[pc];
+    const int tid = threadIdx.x;
+    const int lc = tid & 7, lr = tid >> 3;            // load role: x chunk (8 voxels), row pair
+    const unsigned G = gridDim.x;
+    const int16_t *in = static_cast<const int16_t *>(p.in);
+    int16_t *out = static_cast<int16_t *>(p.out);
+
+    auto load = [&](unsigned t, uint4 &a, uint4 &b) {
+        a = make_uint4(0u, 0u, 0u, 0u);
+        b = a;
+        if (t >= ntiles) return;
+        const unsigned t2 = t / tiles_x;
+        const int tx0 = (int)(t - t2 * tiles_x) * 64;
+        const unsigned oc = t2 / tiles_q;
+        const int tq0 = (int)(t2 - oc * tiles_q) * 64;
+        const int ic = fc ? nc - 1 - (int)oc : (int)oc;
+        if (tx0 + 8 * lc < nxin && tq0 + 2 * lr < nq) {
+            const int16_t *src = in + (size_t)ic * sc_in + (size_t)(tq0 + 2 * lr) * sq + (size_t)(tx0 + 8 * lc);
+            a = __ldg(reinterpret_cast<const uint4 *>(src));
+            b = __ldg(reinterpret_cast<const uint4 *>(src + sq));
+        }
+    };
+    uint4 ra[DEPTH], rb[DEPTH];
+#pragma unroll
+    for (int d = 0; d < DEPTH; ++d) load(blockIdx.x + (unsigned)d * G, ra[d], rb[d]);
+
+    const unsigned wcol = (unsigned)(lr ^ (lc << 2));
+    for (unsigned tb = blockIdx.x; tb < ntiles; tb += (unsigned)DEPTH * G) {
+#pragma unroll
+        for (int d = 0; d < DEPTH; ++d) {
+            const unsigned t = tb + (unsigned)d * G;
+            if (t >= ntiles) break;
+            {
+                const unsigned aw[4] = {ra[d].x, ra[d].y, ra[d].z, ra[d].w}, bw[4] = {rb[d].x, rb[d].y, rb[d].z, rb[d].w};
+                unsigned *row = T + (unsigned)(8 * lc) * 32u + wcol;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    row[(2 * i) * 32] = __byte_perm(aw[i], bw[i], 0x5410);        // (a[q][x],   a[q+1][x])
+                    row[(2 * i + 1) * 32] = __byte_perm(aw[i], bw[i], 0x7632);    // (a[q][x+1], a[q+1][x+1])
+                }
+            }
+            load(t + (unsigned)DEPTH * G, ra[d], rb[d]);
+            __syncthreads();
+            const unsigned t2 = t / tiles_x;
+            const int tx0 = (int)(t - t2 * tiles_x) * 64;
+            const unsigned oc = t2 / tiles_q;
+            const int tq0 = (int)(t2 - oc * tiles_q) * 64;
+            const int g = tid & 7;
+            const int qcol = tq0 + 8 * g;
+            if (qcol < nq) {
+                int16_t *ob = out + (size_t)oc * sc_out;
+                const bool hi_ok = qcol + 4 < nq;            // always true when W16
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int x = (tid >> 3) + 32 * h;
+                    if (tx0 + x < nxin) {
+                        uint4 w = *reinterpret_cast<const uint4 *>(T + x * 32 + 4 * (g ^ (x >> 3)));
+                        if (f2) w = make_uint4(swap_halves(w.w), swap_halves(w.z), swap_halves(w.y), swap_halves(w.x));
+                        const int xo = fa ? nxin - 1 - (tx0 + x) : tx0 + x;
+                        int16_t *orow = ob + (size_t)xo * sa;
+                        if (W16) {
+                            *reinterpret_cast<uint4 *>(orow + (f2 ? nq - 8 - qcol : qcol)) = w;
+                        } else if (!f2) {
+                            *reinterpret_cast<uint2 *>(orow + qcol) = make_uint2(w.x, w.y);
+                            if (hi_ok) *reinterpret_cast<uint2 *>(orow + qcol + 4) = make_uint2(w.z, w.w);
+                        } else {                              // reversed: voxels q..q+3 are the upper half of w
+                            *reinterpret_cast<uint2 *>(orow + (nq - 4 - qcol)) = make_uint2(w.z, w.w);
+                            if (hi_ok) *reinterpret_cast<uint2 *>(orow + (nq - 8 - qcol)) = make_uint2(w.x, w.y);
+                        }
+                    }
+                }
+            }
+            __syncthreads();
+        }
     }
 }
 

@@ -89,9 +89,11 @@ def test_ffs_permutation_bit_exact(cuda_device, case, dtype):
 
 
 @pytest.mark.parametrize("case", list(kernels.FFS_PERMUTATIONS))
-@pytest.mark.parametrize("shape", [(36, 44, 72), (6, 10, 64), (130, 66, 200), (2, 2, 8)])
+@pytest.mark.parametrize("shape", [(36, 44, 72), (6, 10, 64), (130, 66, 200), (2, 2, 8),
+                                   (40, 72, 88), (8, 8, 8), (64, 64, 64), (72, 136, 200), (16, 128, 192), (12, 20, 64), (68, 4, 136)])
 def test_ffs_permutation_vector_paths_bit_exact(cuda_device, case, shape):
-    """Even sizes take the 16-byte row copy / 64x64 2x2-register transpose kernels (int16 only)."""
+    """Even sizes take the 16-byte row copy / 64x64 2x2-register transpose kernels (int16 only); sizes that are
+    multiples of 8 take the 16-byte swizzled transpose (full and partial 64x64 tiles)."""
     rng = np.random.default_rng(5)
     a = rng.integers(-32768, 32767, size=shape).astype(np.int16)
     perm, flip = kernels.FFS_PERMUTATIONS[case]
