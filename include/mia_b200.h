@@ -160,6 +160,40 @@ int mia_warp_dvf(const void *d_mov, int mov_dtype, const int mdims[3], const flo
 int mia_sample_field_points(const float *d_field, const int dims[3], int channels, const double *d_pts, long long n,
                             double scale, double *d_out, void *stream);
 
+/*
+ * SURVEY N3 -- dose on an image lattice under an ROI mask, and its dose-volume statistics.
+ *
+ * Replaces Dose.compute_roi_dose_array (structure/dose.py:738-772: sitk.ResampleImageFilter, reference image =
+ * the CT, sitkLinear, default pixel 0.0, then dose_arr[np.where(mask_arr > 0)]) and the NumPy reductions of
+ * Dose.compute_roi_dose_statistics (structure/dose.py:774-816: min / max / mean / median / std, np.percentile,
+ * counts below dose levels).
+ *
+ * mia_mask_scan counts the non-zero bytes of d_mask (uint8, [z][y][x] on the output lattice `odims`) per
+ * 4096-voxel chunk, scans the counts into the workspace and writes the total to *d_total (device).
+ * mia_resample_masked then samples ONLY the masked voxels (same arithmetic, inside rule and background as
+ * mia_resample_rigid, value kept as unrounded float32) and writes them compacted in C order -- the order of
+ * np.where -- to d_out[0 .. total).  The workspace must be the one mia_mask_scan filled for the same mask.
+ */
+size_t mia_mask_workspace_bytes(const int odims[3]);
+int mia_mask_scan(const unsigned char *d_mask, const int odims[3], unsigned long long *d_total, void *d_ws,
+                  size_t ws_bytes, void *stream);
+int mia_resample_masked(const void *d_mov, int mov_dtype, const int mdims[3], const unsigned char *d_mask,
+                        const int odims[3], const double A[12], double background, int mode, const void *d_ws,
+                        size_t ws_bytes, float *d_out, void *stream);
+
+/*
+ * Statistics of a compact float32 device sample of n > 0 values.  levels (HOST, ascending, <= 64) and ranks
+ * (HOST, 0-based order-statistic indices < n, <= 64) are copied by the call.  d_result (device, float64):
+ *   [0] min  [1] max  [2] sum  [3] mean  [4] sum (x - mean)^2  [5] n
+ *   [6 .. 6 + n_levels)                      number of values < levels[l]
+ *   [6 + n_levels .. 6 + n_levels + n_ranks) the ranks[r]-th smallest value (exact: three-pass radix select)
+ * np.percentile(x, q) = lerp of the order statistics floor / ceil of q / 100 * (n - 1); np.std = sqrt([4] / n).
+ */
+size_t mia_sample_stats_workspace_bytes(void);
+int mia_sample_stats(const float *d_values, unsigned long long n, const float *levels, int n_levels,
+                     const unsigned long long *ranks, int n_ranks, double *d_result, void *d_ws, size_t ws_bytes,
+                     void *stream);
+
 /* Page-locked host buffers for the *_host entry point (a NumPy array can wrap them). */
 void *mia_host_alloc(size_t bytes);
 int mia_host_free(void *p);

@@ -40,6 +40,12 @@ SIGNATURES = {
     "mia_optimizer_read": (_i, [_vp, _dp, _dp, _ip, _ip, _ip, _dp, _dp, _dp, _i, _vp]),
     "mia_warp_dvf": (_i, [_vp, _i, _ip, _vp, _vp, _i, _ip, _dp, _dp, _d, _i, _vp]),
     "mia_sample_field_points": (_i, [_vp, _ip, _i, _vp, _c.c_longlong, _d, _vp, _vp]),
+    "mia_mask_workspace_bytes": (_sz, [_ip]),
+    "mia_mask_scan": (_i, [_vp, _ip, _vp, _vp, _sz, _vp]),
+    "mia_resample_masked": (_i, [_vp, _i, _ip, _vp, _ip, _dp, _d, _i, _vp, _sz, _vp, _vp]),
+    "mia_sample_stats_workspace_bytes": (_sz, []),
+    "mia_sample_stats": (_i, [_vp, _c.c_ulonglong, _c.POINTER(_c.c_float), _i, _c.POINTER(_c.c_ulonglong), _i, _vp,
+                              _vp, _sz, _vp]),
     "mia_host_alloc": (_vp, [_sz]),
     "mia_host_free": (_i, [_vp]),
 }

@@ -17,6 +17,7 @@
 #include "mia_tile.cuh"
 #include "mia_tile_multi.cuh"
 #include "mia_dvf.cuh"
+#include "mia_dose.cuh"
 
 using namespace mia;
 
@@ -580,3 +581,4 @@ int mia_mi_from_hist(const unsigned int *d_hist, int bins, int n_mats, double *d
 
 #include "mia_host_api.inl"
 #include "mia_dvf.inl"
+#include "mia_dose.inl"

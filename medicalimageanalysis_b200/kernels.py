@@ -238,6 +238,104 @@ def sample_field_points(field, points_xyz, scale=1.0, out=None):
     return out
 
 
+def _mask_u8(mask, shape, device):
+    if isinstance(mask, np.ndarray):
+        mask = torch.from_numpy(np.ascontiguousarray(mask))
+    if not isinstance(mask, torch.Tensor):
+        raise TypeError("mask must be a NumPy array or a torch.Tensor [z, y, x]")
+    if tuple(mask.shape) != tuple(shape):
+        raise ValueError("mask shape %s != lattice shape %s" % (tuple(mask.shape), tuple(shape)))
+    mask = mask.to(device)
+    if mask.dtype != torch.uint8:
+        mask = (mask > 0).to(torch.uint8)          # the reference's test is `mask_arr > 0` (structure/dose.py:767)
+    return mask.contiguous()
+
+
+def resample_masked(mov, A, mask, background=0.0, mode="itk"):
+    """``resample(mov, A, mask.shape)[mask > 0]`` without resampling the unmasked voxels: the masked samples as a
+    compact float32 device tensor in C order (``np.where`` order; ``structure/dose.py:760-770``)."""
+    lib = _lib.load()
+    mov = _vol(mov, "mov")
+    mask = _mask_u8(mask, mask.shape, mov.device)
+    if mask.dim() != 3:
+        raise ValueError("mask must be 3-D [z, y, x]")
+    od = i3((mask.shape[2], mask.shape[1], mask.shape[0]))
+    A = _mats(A)
+    nbytes = int(lib.mia_mask_workspace_bytes(od))
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=mov.device)
+    total = torch.zeros(1, dtype=torch.int64, device=mov.device)
+    with torch.cuda.device(mov.device):
+        check(lib.mia_mask_scan(mask.data_ptr(), od, total.data_ptr(), ws.data_ptr(), nbytes, _stream(mov)))
+        n = int(total.item())                      # the one synchronisation: the output size
+        out = torch.empty(n, dtype=torch.float32, device=mov.device)
+        if n:
+            check(lib.mia_resample_masked(mov.data_ptr(), _DT[mov.dtype], _dims(mov), mask.data_ptr(), od,
+                                          darr(A.ravel()), float(background), _MODE[mode], ws.data_ptr(), nbytes,
+                                          out.data_ptr(), _stream(mov)))
+    return out
+
+
+def percentile_ranks(n, qs):
+    """Order-statistic indices (floor, ceil) and lerp weight of ``np.percentile(x, q)`` (method 'linear') for a
+    sample of ``n`` values."""
+    lo, hi, t = [], [], []
+    for q in qs:
+        pos = float(q) / 100.0 * (n - 1)
+        f = int(np.floor(pos))
+        lo.append(f)
+        hi.append(min(f + 1, n - 1))
+        t.append(pos - f)
+    return lo, hi, t
+
+
+def sample_statistics(values, percentiles=(), levels=()):
+    """min / max / mean / std (population, two-pass like ``np.std``) / ``np.percentile`` values / counts below each
+    level of a compact float32 device sample, from ``mia_sample_stats`` (moments + exact radix select)."""
+    lib = _lib.load()
+    if not (isinstance(values, torch.Tensor) and values.is_cuda and values.dtype == torch.float32 and values.dim() == 1):
+        raise TypeError("values must be a 1-D CUDA float32 tensor")
+    values = values.contiguous()
+    n = int(values.numel())
+    if n == 0:
+        raise ValueError("empty sample")
+    levels = [float(v) for v in levels]
+    if levels != sorted(levels):
+        raise ValueError("levels must ascend")
+    lo, hi, t = percentile_ranks(n, percentiles)
+    ranks = lo + hi
+    L, R = len(levels), len(ranks)
+    nbytes = int(lib.mia_sample_stats_workspace_bytes())
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=values.device)
+    res = torch.zeros(6 + L + R, dtype=torch.float64, device=values.device)
+    lv = (ctypes.c_float * max(L, 1))(*levels)
+    rk = (ctypes.c_ulonglong * max(R, 1))(*ranks)
+    with torch.cuda.device(values.device):
+        check(lib.mia_sample_stats(values.data_ptr(), n, lv, L, rk, R, res.data_ptr(), ws.data_ptr(), nbytes,
+                                   _stream(values)))
+    r = res.cpu().numpy()
+    os_ = r[6 + L:]
+    P = len(lo)
+    pct = []
+    for i in range(P):
+        a, b = float(os_[i]), float(os_[P + i])
+        # numpy's _lerp: a + (b - a) * t, evaluated from b when t >= 0.5
+        pct.append(b - (b - a) * (1.0 - t[i]) if t[i] >= 0.5 else a + (b - a) * t[i])
+    return {"count": n, "min": float(r[0]), "max": float(r[1]), "sum": float(r[2]), "mean": float(r[3]),
+            "std": float(np.sqrt(r[4] / n)), "percentiles": pct, "below": [float(v) for v in r[6:6 + L]]}
+
+
+def dose_statistics(mov, A, mask, d_values, levels, background=0.0, mode="itk"):
+    """The numbers of ``Dose.compute_roi_dose_statistics`` (``structure/dose.py:774-816``): D-values are
+    ``np.percentile(sample, 100 - d)``; the median is the 50th percentile."""
+    sample = resample_masked(mov, A, mask, background=background, mode=mode)
+    qs = [100.0 - d for d in d_values] + [50.0]
+    st = sample_statistics(sample, percentiles=qs, levels=levels)
+    st["median"] = st["percentiles"][-1]
+    st["percentiles"] = st["percentiles"][:-1]
+    st["sample"] = sample
+    return st
+
+
 def autocrop_extent(M, p2w_mov, mdims, out_spacing, extent_rule="round"):
     """Host helper mirroring ``geometry.autocrop_extent`` through the C ABI."""
     lib = _lib.load()

@@ -2,16 +2,18 @@
 
 Only the fields and methods the rigid resample path reads are mirrored: ``array, spacing, origin, matrix,
 dimensions, orientation, plane, modality, image_name`` and ``compute_center`` / pixel<->position matrices.
-Tags, ROIs, POIs, persistence and the viewer state are out of scope."""
+The viewer state that drives the off-axis reslice (``Display``, ``update_rotation``) lives in
+``display.py``.  Tags, ROIs, POIs and persistence are out of scope."""
 from __future__ import annotations
 
 import numpy as np
 import torch
 
 from ..geometry import Grid, index_to_physical, physical_to_index
+from .display import OffAxisMixin, VolumeDisplay
 
 
-class Image(object):
+class Image(OffAxisMixin):
     """Duck-typed from any object carrying ``array, image_name, modality, plane, spacing, dimensions,
     orientation, origin, image_matrix`` -- the same construction contract as the reference
     (``structure/image.py:318-350``; DICOM-free producer ``utils/creation.py:257-295``).
@@ -36,6 +38,7 @@ class Image(object):
         self.matrix = np.asarray(image.image_matrix, dtype=np.float32)      # rows = row/col/slice dirs
         self.rois = {}
         self.pois = {}
+        self.display = VolumeDisplay(self)                                  # structure/image.py:348
 
     # -- geometry ------------------------------------------------------------------------------------
     @property
