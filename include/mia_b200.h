@@ -194,6 +194,18 @@ int mia_sample_stats(const float *d_values, unsigned long long n, const float *l
                      const unsigned long long *ranks, int n_ranks, double *d_result, void *d_ws, size_t ws_bytes,
                      void *stream);
 
+/*
+ * SURVEY N4 -- raw volume payloads between files and device memory (MetaImage .raw, the data block of an .npy).
+ * Replaces the host arrays of sitk.ReadImage + GetArrayFromImage (read/mhd.py:157-196), np.load / np.save of
+ * array.npy (structure/image.py:709-735, 804-836) and vtkMetaImageWriter (structure/rigid.py:697-716) for
+ * device-resident volumes.  The payload moves through page-locked 8 MiB staging buffers (four worker threads with two
+ * each, per device), file I/O of one chunk overlapping the PCIe copy of another; both calls synchronise before they return.
+ * `offset` is the byte offset of the payload inside the file (header size of an .npy, 0 for a .raw).
+ */
+int mia_read_file_to_device(const char *path, unsigned long long offset, unsigned long long bytes, void *d_dst, int device);
+int mia_write_file_from_device(const char *path, unsigned long long offset, const void *d_src, unsigned long long bytes,
+                               int truncate, int device);
+
 /* Page-locked host buffers for the *_host entry point (a NumPy array can wrap them). */
 void *mia_host_alloc(size_t bytes);
 int mia_host_free(void *p);

@@ -8,8 +8,9 @@ from .data import Data
 from .structure.image import Image
 from .structure.rigid import Rigid
 from . import utils
+from . import read
 from . import geometry
 from .registration import RegistrationConfig, RegistrationResult
 
 __version__ = "0.1.0"
-__all__ = ["Data", "Image", "Rigid", "utils", "geometry", "RegistrationConfig", "RegistrationResult"]
+__all__ = ["Data", "Image", "Rigid", "utils", "read", "geometry", "RegistrationConfig", "RegistrationResult"]

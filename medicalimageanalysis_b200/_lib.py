@@ -46,6 +46,8 @@ SIGNATURES = {
     "mia_sample_stats_workspace_bytes": (_sz, []),
     "mia_sample_stats": (_i, [_vp, _c.c_ulonglong, _c.POINTER(_c.c_float), _i, _c.POINTER(_c.c_ulonglong), _i, _vp,
                               _vp, _sz, _vp]),
+    "mia_read_file_to_device": (_i, [_c.c_char_p, _c.c_ulonglong, _c.c_ulonglong, _vp, _i]),
+    "mia_write_file_from_device": (_i, [_c.c_char_p, _c.c_ulonglong, _vp, _c.c_ulonglong, _i, _i]),
     "mia_host_alloc": (_vp, [_sz]),
     "mia_host_free": (_i, [_vp]),
 }

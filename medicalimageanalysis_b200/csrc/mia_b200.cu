@@ -582,3 +582,4 @@ int mia_mi_from_hist(const unsigned int *d_hist, int bins, int n_mats, double *d
 #include "mia_host_api.inl"
 #include "mia_dvf.inl"
 #include "mia_dose.inl"
+#include "mia_io.inl"

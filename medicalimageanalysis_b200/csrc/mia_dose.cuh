@@ -195,22 +195,39 @@ __global__ void __launch_bounds__(256) stats_moments_kernel(const float *v, unsi
     __syncthreads();
     if (!s_last) return;
     __threadfence();
-    if (tid == 0) {
+    // fixed-order second stage: thread t sums partials t, t + 256, ...; then a fixed tree over the 256 threads
+    {
+        __shared__ double f_sum[256], f_min[256], f_max[256];
         double s = 0.0, a = INFINITY, b = -INFINITY;
-        for (unsigned g = 0; g < gridDim.x; ++g) {
+        for (unsigned g = tid; g < gridDim.x; g += 256) {
             s += __ldcg(ws.part + 4 * g);
             a = fmin(a, __ldcg(ws.part + 4 * g + 1));
             b = fmax(b, __ldcg(ws.part + 4 * g + 2));
         }
-        result[0] = a; result[1] = b; result[2] = s;
-        result[3] = n ? s / (double)n : 0.0;
-        result[5] = (double)n;
-        *ws.ticket = 0u;
+        f_sum[tid] = s; f_min[tid] = a; f_max[tid] = b;
+        __syncthreads();
+        for (int o = 128; o > 0; o >>= 1) {
+            if (tid < o) {
+                f_sum[tid] += f_sum[tid + o];
+                f_min[tid] = fmin(f_min[tid], f_min[tid + o]);
+                f_max[tid] = fmax(f_max[tid], f_max[tid + o]);
+            }
+            __syncthreads();
+        }
+        if (tid == 0) {
+            result[0] = f_min[0]; result[1] = f_max[0]; result[2] = f_sum[0];
+            result[3] = n ? f_sum[0] / (double)n : 0.0;
+            result[5] = (double)n;
+            *ws.ticket = 0u;
+        }
     }
-    if (tid < n_levels) {
+    // level counts: warp w takes levels w, w + 8, ...; integer sums, any order
+    for (int l = tid >> 5; l < n_levels; l += 8) {
         unsigned long long c = 0;
-        for (unsigned g = 0; g < gridDim.x; ++g) c += __ldcg(ws.part_below + (size_t)g * kMaxLevels + tid);
-        result[6 + tid] = (double)c;
+        for (unsigned g = tid & 31; g < gridDim.x; g += 32) c += __ldcg(ws.part_below + (size_t)g * kMaxLevels + l);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+        if ((tid & 31) == 0) result[6 + l] = (double)c;
     }
 }
 
@@ -248,34 +265,66 @@ __global__ void __launch_bounds__(256) stats_hist1_kernel(const float *v, unsign
     __syncthreads();
     if (!s_last) return;
     __threadfence();
-    if (tid == 0) {
+    {
+        __shared__ double f_sum[256];
         double s = 0.0;
-        for (unsigned g = 0; g < gridDim.x; ++g) s += __ldcg(ws.part_ssq + g);
-        result[4] = s;
-        *ws.ticket = 0u;
+        for (unsigned g = tid; g < gridDim.x; g += 256) s += __ldcg(ws.part_ssq + g);
+        f_sum[tid] = s;
+        __syncthreads();
+        for (int o = 128; o > 0; o >>= 1) {
+            if (tid < o) f_sum[tid] += f_sum[tid + o];
+            __syncthreads();
+        }
+        if (tid == 0) {
+            result[4] = f_sum[0];
+            *ws.ticket = 0u;
+        }
     }
     (void)n_levels;
 }
 
-// Resolve one radix level for every rank: walk the histogram of the rank's current prefix until the cumulative
-// count passes the remaining rank.  One thread per rank (histograms are at most 4096 bins).
-__global__ void stats_resolve_kernel(StatsWs ws, int n_ranks, int level, int n_levels, double *result)
+// Resolve one radix level for every rank: find the bin of the rank's current histogram in which the cumulative
+// count passes the remaining rank.  One block per rank: each thread owns nb / 256 consecutive bins, a block scan of
+// the per-thread totals locates the owning thread, which then walks its own bins.
+__global__ void __launch_bounds__(256) stats_resolve_kernel(StatsWs ws, int n_ranks, int level, int n_levels, double *result)
 {
-    const int r = threadIdx.x;
+    __shared__ unsigned long long s_w[8];
+    const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (r >= n_ranks) return;
     const unsigned *h = level == 0 ? ws.hist1 : ws.histn + (size_t)r * 1024;
-    const int nb = level == 0 ? 4096 : 1024;
-    unsigned long long rem = ws.ranks[r];
-    int b = 0;
-    for (; b < nb - 1; ++b) {
-        const unsigned c = __ldcg(h + b);
-        if (rem < c) break;
-        rem -= c;
+    const int per = level == 0 ? 16 : 4;
+    unsigned c[16];
+    unsigned long long mine = 0;
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+        c[e] = e < per ? __ldcg(h + tid * per + e) : 0u;
+        mine += c[e];
     }
-    ws.ranks[r] = rem;
-    const unsigned pre = level == 0 ? (unsigned)b : ((ws.prefix[r] << 10) | (unsigned)b);
-    ws.prefix[r] = pre;
-    if (level == 2) result[6 + n_levels + r] = (double)key_float(pre);
+    unsigned long long incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_w[warp] = incl;
+    __syncthreads();
+    unsigned long long before = incl - mine;
+    for (int q = 0; q < warp; ++q) before += s_w[q];
+    const unsigned long long rem = ws.ranks[r];
+    __syncthreads();                                   // everyone has read ranks[r] before the owner rewrites it
+    if (rem >= before && rem < before + mine) {        // exactly one thread (rank < total count)
+        unsigned long long left = rem - before;
+        int e = 0;
+        for (; e < per - 1; ++e) {
+            if (left < c[e]) break;
+            left -= c[e];
+        }
+        const unsigned b = (unsigned)(tid * per + e);
+        ws.ranks[r] = left;
+        const unsigned pre = level == 0 ? b : ((ws.prefix[r] << 10) | b);
+        ws.prefix[r] = pre;
+        if (level == 2) result[6 + n_levels + r] = (double)key_float(pre);
+    }
 }
 
 // Passes C / D: 10-bit histograms below each rank's prefix (pbits = 12 or 22 leading bits already fixed).

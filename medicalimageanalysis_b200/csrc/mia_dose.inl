@@ -134,17 +134,17 @@ int mia_sample_stats(const float *d_values, unsigned long long n, const float *l
     CUDA_TRY(cudaMemsetAsync(ws + w.ticket, 0, w.total - w.ticket, s));
     if (n_levels) CUDA_TRY(cudaMemcpyAsync(k.levels, levels, sizeof(float) * n_levels, cudaMemcpyHostToDevice, s));
     if (n_ranks) CUDA_TRY(cudaMemcpyAsync(k.ranks, ranks, sizeof(unsigned long long) * n_ranks, cudaMemcpyHostToDevice, s));
-    unsigned long long gb = (n + 255) / 256;
+    unsigned long long gb = (n + 256 * 8 - 1) / (256 * 8);            // ~8 values per thread before adding blocks
     const unsigned grid = (unsigned)(gb < kStatsGridMax ? gb : kStatsGridMax);
     mia::stats_moments_kernel<<<grid, 256, 0, s>>>(d_values, n, n_levels, k, d_result);
     mia::stats_hist1_kernel<<<grid, 256, 0, s>>>(d_values, n, n_levels, k, d_result);
     if (n_ranks) {
-        mia::stats_resolve_kernel<<<1, mia::kMaxRanks, 0, s>>>(k, n_ranks, 0, n_levels, d_result);
+        mia::stats_resolve_kernel<<<n_ranks, 256, 0, s>>>(k, n_ranks, 0, n_levels, d_result);
         mia::stats_histn_kernel<<<grid, 256, 0, s>>>(d_values, n, k, n_ranks, 12);
-        mia::stats_resolve_kernel<<<1, mia::kMaxRanks, 0, s>>>(k, n_ranks, 1, n_levels, d_result);
+        mia::stats_resolve_kernel<<<n_ranks, 256, 0, s>>>(k, n_ranks, 1, n_levels, d_result);
         CUDA_TRY(cudaMemsetAsync(k.histn, 0, sizeof(unsigned) * 1024 * mia::kMaxRanks, s));
         mia::stats_histn_kernel<<<grid, 256, 0, s>>>(d_values, n, k, n_ranks, 22);
-        mia::stats_resolve_kernel<<<1, mia::kMaxRanks, 0, s>>>(k, n_ranks, 2, n_levels, d_result);
+        mia::stats_resolve_kernel<<<n_ranks, 256, 0, s>>>(k, n_ranks, 2, n_levels, d_result);
     }
     CUDA_TRY(cudaGetLastError());
     return MIA_OK;

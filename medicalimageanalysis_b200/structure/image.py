@@ -6,6 +6,8 @@ The viewer state that drives the off-axis reslice (``Display``, ``update_rotatio
 ``display.py``.  Tags, ROIs, POIs and persistence are out of scope."""
 from __future__ import annotations
 
+import os
+
 import numpy as np
 import torch
 
@@ -65,3 +67,35 @@ class Image(OffAxisMixin):
 
     def numpy(self):
         return self.array.cpu().numpy()
+
+    # -- persistence -------------------------------------------------------------------------
+    _NOT_SAVED = ('rois', 'pois', 'tags', 'array', 'display')           # structure/image.py:726
+
+    def save_image(self, path, rois=True, pois=True):
+        """``structure/image.py:709-741``: ``info.p`` (one-row DataFrame of the scalar fields) + ``array.npy``, the
+        latter written from the device (same bytes as ``np.save``).  ROI / POI folders are out of scope."""
+        import pandas as pd
+        from ..read.npy import save_npy_from_device
+        column_names = [name for name in self.__dict__.keys() if name not in self._NOT_SAVED]
+        df = pd.DataFrame(index=[0], columns=column_names)
+        for name in column_names:
+            df.at[0, name] = getattr(self, name)
+        df.to_pickle(os.path.join(path, 'info.p'))
+        if self.array.is_cuda:
+            save_npy_from_device(os.path.join(path, 'array.npy'), self.array)
+        else:
+            np.save(os.path.join(path, 'array.npy'), self.array.numpy(), allow_pickle=True)
+
+    def load_image(self, image_path, rois=True, pois=True, device=None):
+        """``structure/image.py:804-836``: ``array.npy`` lands in HBM without a pageable host copy."""
+        import pandas as pd
+        from ..read.npy import load_npy_to_device
+        device = device or self.array.device
+        if torch.device(device).type == "cuda":
+            self.array = load_npy_to_device(os.path.join(image_path, 'array.npy'), device=device)
+        else:
+            self.array = torch.from_numpy(np.load(os.path.join(image_path, 'array.npy'), allow_pickle=True))
+        info = pd.read_pickle(os.path.join(image_path, 'info.p'))
+        for column in list(info.columns):
+            setattr(self, column, info.at[0, column])
+        self.display = VolumeDisplay(self)

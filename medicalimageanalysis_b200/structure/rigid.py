@@ -172,6 +172,14 @@ class Rigid(object):
         out = kernels.resample(mov_img.array, A, (dims[2], dims[1], dims[0]), background=BACKGROUND, mode="vtk")
         return ResampledImage(out, origin, tuple(ref_img.spacing))
 
+    def export_image(self, path=None):
+        """``structure/rigid.py:697-716`` (``vtkMetaImageWriter``): the aligned volume as an .mhd / .raw pair, the
+        payload written from the device."""
+        if self.moving_name is not None and path is not None:
+            from ..read.mhd import write_mhd
+            image = self.create_image()
+            write_mhd(path, image.array, spacing=image.spacing, origin=image.origin)
+
     # -- parameter updates -------------------------------------------------------------------------
     def retrieve_center(self, slice_plane=None, location=None):
         """``structure/rigid.py:786-812``: centre of the FIXED image, optionally projected on a slice plane."""

@@ -12,8 +12,14 @@ from ... import kernels
 from ...registration import RegistrationConfig, RegistrationResult, register_rigid as _register
 from ...structure.rigid import BACKGROUND, ResampledImage
 
-__all__ = ["resample_rigid", "resample_to_reference", "reorient_ffs", "verify_axial_orientation", "metric_ssd",
+__all__ = ["matrix_from_dicom_reg", "resample_rigid", "resample_to_reference", "reorient_ffs", "verify_axial_orientation", "metric_ssd",
            "metric_mi", "register_rigid", "RegistrationConfig", "RegistrationResult"]
+
+
+def matrix_from_dicom_reg(values):
+    """DICOM REG ``FrameOfReferenceTransformationMatrix`` (3006,00C6), 16 numbers row-major, to the moving matrix the
+    reference stores (``read/dicom.py:1751-1763``): ``moving_matrix = inv(matrix.reshape(4, 4))``."""
+    return np.linalg.inv(np.asarray(values, dtype=np.float64).reshape(4, 4))
 
 
 def resample_rigid(moving, reference, matrix, background=BACKGROUND, inverse=False):
