@@ -206,6 +206,15 @@ int mia_read_file_to_device(const char *path, unsigned long long offset, unsigne
 int mia_write_file_from_device(const char *path, unsigned long long offset, const void *d_src, unsigned long long bytes,
                                int truncate, int device);
 
+/*
+ * SURVEY N5 -- one level of a multi-resolution pyramid (what "NumberOfResolutions" asks of Elastix,
+ * utils/deformable/simpleitk.py:150-163): d_out[k][j][i] = mean of the factors[0] x factors[1] x factors[2] block of
+ * d_in starting at (i, j, k) * factors (fewer voxels on the high edges), int16 rounded half-up.  factors and idims
+ * are (x, y, z); output dims = ceil(idims / factors).  The level's lattice: spacing * factors, origin moved by
+ * half a (factor - 1) voxel along each axis (geometry.pyramid_grid).
+ */
+int mia_shrink_mean(const void *d_in, int dtype, const int idims[3], void *d_out, const int factors[3], void *stream);
+
 /* Page-locked host buffers for the *_host entry point (a NumPy array can wrap them). */
 void *mia_host_alloc(size_t bytes);
 int mia_host_free(void *p);

@@ -48,6 +48,7 @@ SIGNATURES = {
                               _vp, _sz, _vp]),
     "mia_read_file_to_device": (_i, [_c.c_char_p, _c.c_ulonglong, _c.c_ulonglong, _vp, _i]),
     "mia_write_file_from_device": (_i, [_c.c_char_p, _c.c_ulonglong, _vp, _c.c_ulonglong, _i, _i]),
+    "mia_shrink_mean": (_i, [_vp, _i, _ip, _vp, _ip, _vp]),
     "mia_host_alloc": (_vp, [_sz]),
     "mia_host_free": (_i, [_vp]),
 }

@@ -18,6 +18,7 @@
 #include "mia_tile_multi.cuh"
 #include "mia_dvf.cuh"
 #include "mia_dose.cuh"
+#include "mia_pyramid.cuh"
 
 using namespace mia;
 
@@ -583,3 +584,4 @@ int mia_mi_from_hist(const unsigned int *d_hist, int bins, int n_mats, double *d
 #include "mia_dvf.inl"
 #include "mia_dose.inl"
 #include "mia_io.inl"
+#include "mia_pyramid.inl"

@@ -23,7 +23,7 @@ import numpy as np
 __all__ = [
     "Grid", "euler_xyz_matrix", "euler_from_matrix_ZXY", "itk_euler_matrix", "pivot_transform",
     "translation_transform", "index_to_physical", "physical_to_index", "compose_index_matrix",
-    "autocrop_extent", "params_to_matrix", "slab_moving_zrange", "is_signed_permutation",
+    "autocrop_extent", "params_to_matrix", "slab_moving_zrange", "is_signed_permutation", "pyramid_grid",
 ]
 
 
@@ -227,3 +227,13 @@ def is_signed_permutation(A: np.ndarray, tol: float = 0.0):
     if sorted(perm) != [0, 1, 2]:
         return None
     return tuple(perm), tuple(flip)
+
+
+def pyramid_grid(grid: Grid, factors, convention: str = "itk") -> Grid:
+    """Lattice of a block-mean pyramid level: dims = ceil(dims / f), spacing * f, and the origin moved
+    to the centre of the first block, i.e. by (f - 1) / 2 voxels along each index axis."""
+    f = np.asarray([int(v) for v in factors], dtype=np.float64)
+    dims = tuple(int(-(-d // int(ff))) for d, ff in zip(grid.dims, f))
+    shift = index_to_physical(grid, convention)[:3, :3] @ ((f - 1.0) / 2.0)
+    origin = tuple(np.asarray(grid.origin, dtype=np.float64) + shift)
+    return Grid(dims, tuple(np.asarray(grid.spacing) * f), origin, grid.matrix)

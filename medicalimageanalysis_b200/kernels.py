@@ -336,6 +336,19 @@ def dose_statistics(mov, A, mask, d_values, levels, background=0.0, mode="itk"):
     return st
 
 
+def shrink_mean(vol, factors, out=None):
+    """One pyramid level: block mean over ``factors`` = (fx, fy, fz) voxels (``mia_shrink_mean``)."""
+    lib = _lib.load()
+    vol = _vol(vol, "vol")
+    f = tuple(int(v) for v in factors)
+    oshape = tuple((vol.shape[a] + ff - 1) // ff for a, ff in zip((0, 1, 2), (f[2], f[1], f[0])))
+    if out is None:
+        out = torch.empty(oshape, dtype=vol.dtype, device=vol.device)
+    with torch.cuda.device(vol.device):
+        check(lib.mia_shrink_mean(vol.data_ptr(), _DT[vol.dtype], _dims(vol), out.data_ptr(), i3(f), _stream(vol)))
+    return out
+
+
 def autocrop_extent(M, p2w_mov, mdims, out_spacing, extent_rule="round"):
     """Host helper mirroring ``geometry.autocrop_extent`` through the C ABI."""
     lib = _lib.load()

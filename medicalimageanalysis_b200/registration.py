@@ -112,8 +112,10 @@ def _intensity_range(t):
     return float(t.min().item()), float(t.max().item())
 
 
-def register_rigid(fixed, moving, params0=None, cfg: RegistrationConfig | None = None):
+def register_rigid(fixed, moving, params0=None, cfg: RegistrationConfig | None = None, center=None):
     """Register ``moving`` to ``fixed`` (both ``structure.Image``-like with CUDA arrays) entirely on the GPU.
+    ``center``: rotation pivot in mm (default: the fixed image centre); the multi-resolution driver pins it to the
+    full-resolution centre so that parameters carry over between levels unchanged.
 
     Returns a ``RegistrationResult``; ``result.matrix`` maps fixed physical -> moving physical, i.e. it is
     what ``Rigid.matrix`` holds (``structure/rigid.py:674-686``)."""
@@ -124,7 +126,7 @@ def register_rigid(fixed, moving, params0=None, cfg: RegistrationConfig | None =
     cfg = cfg or RegistrationConfig()
     params0 = np.zeros(6) if params0 is None else np.asarray(params0, dtype=np.float64)
     dev = fixed.array.device
-    center = np.asarray(fixed.compute_center(), dtype=np.float64)
+    center = np.asarray(fixed.compute_center() if center is None else center, dtype=np.float64)
     p2w = G.index_to_physical(fixed.grid, "itk")
     w2p = G.physical_to_index(moving.grid, "itk")
     is_ssd = cfg.metric == "ssd"
@@ -189,3 +191,59 @@ def register_rigid(fixed, moving, params0=None, cfg: RegistrationConfig | None =
                               converged=bool(conv.value), n_reject=int(nrej.value), cost_history=hc[:iters.value],
                               param_history=hp[:iters.value], scale_history=hs[:iters.value],
                               evaluations=N_PROBES * int(iters.value))
+
+
+class PyramidLevel(object):
+    """An ``Image``-like view of one pyramid level: ``array`` (device), ``grid``, ``spacing``, ``origin``, ``matrix``."""
+
+    def __init__(self, array, grid):
+        self.array, self.grid = array, grid
+        self.spacing, self.origin, self.matrix = np.asarray(grid.spacing), np.asarray(grid.origin), grid.matrix
+        self.dimensions = np.asarray(array.shape)
+
+    def compute_center(self):
+        d = self.grid.dims
+        idx = np.array([int(d[0] / 2), int(d[1] / 2), int(d[2] / 2), 1.0])
+        return (G.index_to_physical(self.grid, "itk") @ idx)[:3]
+
+
+def pyramid_level(image, factors):
+    """Block-mean level of ``image``.  ``factors`` = (fx, fy, fz); (1, 1, 1) returns a view."""
+    from . import kernels
+    f = tuple(int(v) for v in factors)
+    if f == (1, 1, 1):
+        return PyramidLevel(image.array, image.grid)
+    return PyramidLevel(kernels.shrink_mean(image.array, f), G.pyramid_grid(image.grid, f))
+
+
+def register_rigid_multires(fixed, moving, params0=None, cfg: RegistrationConfig | None = None,
+                            shrink_factors=(4, 2, 1), iterations=None):
+    """Coarse-to-fine ``register_rigid`` over block-mean pyramids of both images -- the "NumberOfResolutions"
+    schedule the reference asks Elastix for (``utils/deformable/simpleitk.py:155``).  ``shrink_factors``: one
+    entry per level, an int (isotropic) or an (fx, fy, fz) triple; ``iterations``: per level (default: ``cfg.iterations``
+    at every level).  The parameters are physical (degrees about the FULL-resolution fixed centre, mm), so each
+    level starts from the previous level's result.  Returns the last level's result with ``extra['levels']``."""
+    import dataclasses
+    cfg = cfg or RegistrationConfig()
+    center = np.asarray(fixed.compute_center(), dtype=np.float64)
+    levels = [(f, f, f) if np.isscalar(f) else tuple(f) for f in shrink_factors]
+    iters = [cfg.iterations] * len(levels) if iterations is None else list(iterations)
+    if len(iters) != len(levels):
+        raise ValueError("iterations must have one entry per level")
+    frange = cfg.frange or (_intensity_range(fixed.array) if cfg.metric == "mi" else None)
+    mrange = cfg.mrange or (_intensity_range(moving.array) if cfg.metric == "mi" else None)
+    params = np.zeros(6) if params0 is None else np.asarray(params0, dtype=np.float64)
+    per_level, evals, res = [], 0, None
+    for f, n_it in zip(levels, iters):
+        fl, ml = pyramid_level(fixed, f), pyramid_level(moving, f)
+        gi = cfg.graph_iters if n_it >= cfg.graph_iters else 0
+        lcfg = dataclasses.replace(cfg, iterations=int(n_it), frange=frange, mrange=mrange, graph_iters=gi)
+        res = register_rigid(fl, ml, params0=params, cfg=lcfg, center=center)
+        params = res.params
+        evals += res.evaluations
+        per_level.append({"factors": f, "dims": fl.grid.dims, "iterations": res.iterations, "params": res.params.copy(),
+                          "cost_first": float(res.cost_history[0]) if len(res.cost_history) else None,
+                          "cost_last": float(res.cost_history[-1]) if len(res.cost_history) else None})
+    res.evaluations = evals
+    res.extra["levels"] = per_level
+    return res

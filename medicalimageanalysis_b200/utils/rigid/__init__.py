@@ -9,11 +9,12 @@ import numpy as np
 
 from ... import geometry as G
 from ... import kernels
-from ...registration import RegistrationConfig, RegistrationResult, register_rigid as _register
+from ...registration import (RegistrationConfig, RegistrationResult, register_rigid as _register,
+                             register_rigid_multires as _register_multires, pyramid_level)
 from ...structure.rigid import BACKGROUND, ResampledImage
 
 __all__ = ["matrix_from_dicom_reg", "resample_rigid", "resample_to_reference", "reorient_ffs", "verify_axial_orientation", "metric_ssd",
-           "metric_mi", "register_rigid", "RegistrationConfig", "RegistrationResult"]
+           "metric_mi", "register_rigid", "register_rigid_multires", "pyramid_level", "RegistrationConfig", "RegistrationResult"]
 
 
 def matrix_from_dicom_reg(values):
@@ -146,3 +147,11 @@ def register_rigid(fixed, moving, params0=None, cfg=None, **kwargs):
     if cfg is None:
         cfg = RegistrationConfig(**kwargs)
     return _register(fixed, moving, params0=params0, cfg=cfg)
+
+
+def register_rigid_multires(fixed, moving, params0=None, cfg=None, shrink_factors=(4, 2, 1), iterations=None, **kwargs):
+    """Coarse-to-fine registration over block-mean pyramids (``registration.register_rigid_multires``)."""
+    if cfg is None:
+        cfg = RegistrationConfig(**kwargs)
+    return _register_multires(fixed, moving, params0=params0, cfg=cfg, shrink_factors=shrink_factors,
+                              iterations=iterations)
