@@ -215,6 +215,22 @@ int mia_write_file_from_device(const char *path, unsigned long long offset, cons
  */
 int mia_shrink_mean(const void *d_in, int dtype, const int idims[3], void *d_out, const int factors[3], void *stream);
 
+/*
+ * SURVEY N5 -- fixed-image masks for the fused metrics (SetMetricFixedMask / elastix SetFixedMask,
+ * utils/deformable/simpleitk.py:116-117, 146-147).  Same arguments as mia_resample_ssd / mia_resample_jointhist
+ * plus d_fixed_mask: uint8 [z][y][x] on the fixed lattice, 0 = the voxel takes no part in the metric (NULL = no
+ * mask).  A masked SSD does not store the resampled volume (d_out must be NULL).
+ */
+int mia_resample_ssd_masked(const void *d_mov, int mov_dtype, const int mdims[3], const void *d_fixed,
+                            int fixed_dtype, const unsigned char *d_fixed_mask, const int odims[3], void *d_out,
+                            int out_dtype, int n_mats, const double *A, const double *d_A, double background, int mode,
+                            double *d_ssd, unsigned long long *d_count, void *d_ws, size_t ws_bytes, void *stream);
+int mia_resample_jointhist_masked(const void *d_mov, int mov_dtype, const int mdims[3], const void *d_fixed,
+                                  int fixed_dtype, const unsigned char *d_fixed_mask, const int odims[3], int n_mats,
+                                  const double *A, const double *d_A, int mode, float fmin, float fmax, float mmin,
+                                  float mmax, int bins, unsigned int *d_hist, unsigned long long *d_count, void *d_ws,
+                                  size_t ws_bytes, void *stream);
+
 /* Page-locked host buffers for the *_host entry point (a NumPy array can wrap them). */
 void *mia_host_alloc(size_t bytes);
 int mia_host_free(void *p);

@@ -241,14 +241,14 @@ void fill_tile(KParams &p)
     p.ntiles = (long long)p.ntx * p.nty * ((p.oz + kTZ - 1) / kTZ);
 }
 
-template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK>
+template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, bool MASK = false>
 int launch_tile(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream_t s)
 {
     using CFG = TileCfg<TM, METRIC>;
     using BOX = typename CFG::BOX;
     constexpr int NST = CFG::NST, MINB = CFG::MINB;
     constexpr bool PREFETCH = CFG::PREFETCH;
-    auto k = tile_kernel<TM, TF, TO, METRIC, STORE, VTK, BOX, NST, MINB, PREFETCH>;
+    auto k = tile_kernel<TM, TF, TO, METRIC, STORE, VTK, BOX, NST, MINB, PREFETCH, MASK>;
     const size_t smem = TileSmem<TM, BOX, NST>::bytes(METRIC == kHist ? p.bins : 0);
     static std::mutex mu;
     static std::map<std::pair<int, size_t>, int> occ;     // (device, smem) -> resident CTAs per SM
@@ -299,6 +299,15 @@ int try_tile_box(int mode, const void *d_mov, const int mdims[3], const double *
     p.magic_fold = 0u - kMagicBits * (unsigned)((BOX::kY + 1) * BOX::kX + 1) * (unsigned)sizeof(TM);
     if (p.ntiles > 0x7fffffffLL) return MIA_OK;
     if ((long long)p.ox * p.oy * kTZ >= 0x7fffffffLL) return MIA_OK;   // in-tile plane offsets are 32-bit
+    if (p.fmask) {
+        // masked metrics exist without a stored output only (SSD / joint histogram inside a registration loop)
+        if constexpr (!STORE && METRIC != kNone) {
+            launched = true;
+            return mode == MIA_MODE_VTK ? launch_tile<TM, TM, TM, METRIC, false, true, true>(map, p, n_mats, s)
+                                        : launch_tile<TM, TM, TM, METRIC, false, false, true>(map, p, n_mats, s);
+        }
+        return MIA_OK;
+    }
     launched = true;
     return mode == MIA_MODE_VTK ? launch_tile<TM, TM, TM, METRIC, STORE, true>(map, p, n_mats, s)
                                 : launch_tile<TM, TM, TM, METRIC, STORE, false>(map, p, n_mats, s);
@@ -322,13 +331,13 @@ template <typename TM> struct MultiCfg;
 template <> struct MultiCfg<int16_t> : MultiCfgT<MIA_MULTI_I16> {};
 template <> struct MultiCfg<float> : MultiCfgT<MIA_MULTI_F32> {};
 
-template <typename TM, bool VTK>
+template <typename TM, bool VTK, bool MASK = false>
 int launch_multi(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream_t s)
 {
     using BOX = typename TileCfg<TM, kSsd>::BOX;
     constexpr int NST = MultiCfg<TM>::NST, G = MultiCfg<TM>::G;
     constexpr int threads = 32 * (kConsumerWarps * G + 1);
-    auto k = tile_multi_kernel<TM, TM, VTK, BOX, NST, G>;
+    auto k = tile_multi_kernel<TM, TM, VTK, BOX, NST, G, MASK>;
     const size_t smem = MultiSmem<TM, BOX, NST, G>::kBytes;
     static std::mutex mu;
     static std::map<int, int> occ;                         // device -> resident CTAs per SM
@@ -377,6 +386,8 @@ int try_multi_t(int mode, const void *d_mov, const int mdims[3], const double *A
     if (p.ntiles > 0x7fffffffLL) return MIA_OK;
     if ((long long)p.ox * p.oy * kTZ >= 0x7fffffffLL) return MIA_OK;
     launched = true;
+    if (p.fmask)
+        return mode == MIA_MODE_VTK ? launch_multi<TM, true, true>(map, p, n_mats, s) : launch_multi<TM, false, true>(map, p, n_mats, s);
     return mode == MIA_MODE_VTK ? launch_multi<TM, true>(map, p, n_mats, s) : launch_multi<TM, false>(map, p, n_mats, s);
 }
 
@@ -496,7 +507,17 @@ int mia_resample_ssd(const void *d_mov, int mov_dtype, const int mdims[3], const
                      const double *A, const double *d_A, double background, int mode, double *d_ssd,
                      unsigned long long *d_count, void *d_ws, size_t ws_bytes, void *stream)
 {
+    return mia_resample_ssd_masked(d_mov, mov_dtype, mdims, d_fixed, fixed_dtype, nullptr, odims, d_out, out_dtype, n_mats, A,
+                                   d_A, background, mode, d_ssd, d_count, d_ws, ws_bytes, stream);
+}
+
+int mia_resample_ssd_masked(const void *d_mov, int mov_dtype, const int mdims[3], const void *d_fixed,
+                            int fixed_dtype, const unsigned char *d_fixed_mask, const int odims[3], void *d_out,
+                            int out_dtype, int n_mats, const double *A, const double *d_A, double background, int mode,
+                            double *d_ssd, unsigned long long *d_count, void *d_ws, size_t ws_bytes, void *stream)
+{
     cudaStream_t s = (cudaStream_t)stream;
+    if (d_out && d_fixed_mask) return fail(MIA_ERR_UNSUPPORTED, "mia_resample_ssd_masked: a masked metric does not store");
     if (!d_ssd || !d_count) return fail(MIA_ERR_ARG, "mia_resample_ssd: null result pointer");
     if (d_out && n_mats != 1) return fail(MIA_ERR_ARG, "mia_resample_ssd: storing needs n_mats == 1");
     if (d_out && out_dtype != mov_dtype)
@@ -506,6 +527,7 @@ int mia_resample_ssd(const void *d_mov, int mov_dtype, const int mdims[3], const
     int rc = metric_common(p, "mia_resample_ssd", d_mov, mov_dtype, mdims, d_fixed, fixed_dtype, odims, n_mats,
                            A, d_A, mode, d_ws, ws_bytes, s, w);
     if (rc) return rc;
+    p.fmask = d_fixed_mask;
     p.out = d_out;
     p.background = (float)background;
     p.d_ssd = d_ssd;
@@ -537,6 +559,16 @@ int mia_resample_jointhist(const void *d_mov, int mov_dtype, const int mdims[3],
                            int bins, unsigned int *d_hist, unsigned long long *d_count, void *d_ws,
                            size_t ws_bytes, void *stream)
 {
+    return mia_resample_jointhist_masked(d_mov, mov_dtype, mdims, d_fixed, fixed_dtype, nullptr, odims, n_mats, A, d_A, mode,
+                                         fmin, fmax, mmin, mmax, bins, d_hist, d_count, d_ws, ws_bytes, stream);
+}
+
+int mia_resample_jointhist_masked(const void *d_mov, int mov_dtype, const int mdims[3], const void *d_fixed,
+                                  int fixed_dtype, const unsigned char *d_fixed_mask, const int odims[3], int n_mats,
+                                  const double *A, const double *d_A, int mode, float fmin, float fmax, float mmin,
+                                  float mmax, int bins, unsigned int *d_hist, unsigned long long *d_count, void *d_ws,
+                                  size_t ws_bytes, void *stream)
+{
     cudaStream_t s = (cudaStream_t)stream;
     if (!d_hist || !d_count) return fail(MIA_ERR_ARG, "mia_resample_jointhist: null result pointer");
     if (bins < 2 || bins > MIA_MAX_BINS) return fail(MIA_ERR_ARG, "mia_resample_jointhist: bins must be 2..%d", MIA_MAX_BINS);
@@ -546,6 +578,7 @@ int mia_resample_jointhist(const void *d_mov, int mov_dtype, const int mdims[3],
     int rc = metric_common(p, "mia_resample_jointhist", d_mov, mov_dtype, mdims, d_fixed, fixed_dtype, odims,
                            n_mats, A, d_A, mode, d_ws, ws_bytes, s, w);
     if (rc) return rc;
+    p.fmask = d_fixed_mask;
     p.d_hist = d_hist;
     p.d_count = d_count;
     p.bins = bins;

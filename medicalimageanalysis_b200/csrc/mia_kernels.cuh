@@ -9,6 +9,7 @@ enum Metric { kNone = 0, kSsd = 1, kHist = 2 };
 struct KParams {
     VolView mov;                 // moving volume
     const void *fixed;           // fixed volume on the output lattice (metrics) or nullptr
+    const unsigned char *fmask;  // optional fixed-image mask on the output lattice (metrics): 0 = voxel ignored
     void *out;                   // resampled output or nullptr
     int ox, oy, oz;              // output lattice
     int ntx, nty;                // tiles along x / y
@@ -107,7 +108,8 @@ __global__ void __launch_bounds__(kThreads) resample_kernel(const KParams p)
 #pragma unroll
         for (int v = 0; v < kV; ++v) {
             float val;
-            const bool live = full || (i0 + v >= 0 && i0 + v < p.ox);
+            bool live = full || (i0 + v >= 0 && i0 + v < p.ox);
+            if (METRIC != kNone && p.fmask && live) live = __ldg(p.fmask + rowbase + i0 + v) != 0;
             const bool in = live && sample_voxel<TM, CLOSED>(mov, nx, ny, nz, r, v, val);
             if (STORE) o.v[v] = in ? to_out<TO>(val, p.round_mode) : to_out<TO>(p.background, p.round_mode);
             if (METRIC == kSsd && in) {

@@ -341,6 +341,19 @@ __device__ __forceinline__ void load_fixed(float (&fv)[kTZ], const TF *fp, int n
     }
 }
 
+// Fixed-image mask of this thread's column in one tile: bit kz set = voxel (i, j, k0 + kz) takes part in the metric.
+__device__ __forceinline__ unsigned load_mask_bits(const unsigned char *mp, int nk, unsigned plane)
+{
+    unsigned bits = 0u;
+#pragma unroll
+    for (int kz = 0; kz < kTZ; ++kz) {
+        asm("" : "+l"(mp));
+        if (kz < nk && __ldg(mp) != 0) bits |= 1u << kz;
+        mp += plane;
+    }
+    return bits;
+}
+
 // One consumer thread's share of one tile whose box is resident in shared memory: the 8 z planes of
 // output voxel column (i0 + lane, j0 + warp), as 4 packed pairs.  BORDER adds the inside test and the
 // coordinate clamp (== VTK/ITK index clamp: the clamped coordinate has weight 0 on the tap beyond the edge,
@@ -350,11 +363,12 @@ __device__ __forceinline__ void load_fixed(float (&fv)[kTZ], const TF *fp, int n
 // (valid on entry, left alone: the multi-matrix kernel reuses them for every matrix of the tile).
 enum { kFxLoadHere = 0, kFxPrefetchNext = 1, kFxKeep = 2 };
 
-template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, bool BORDER, class BOX, int FX>
+// MASK: only the voxels whose bit is set in `mbits` (load_mask_bits) count for the metric.
+template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, bool BORDER, class BOX, int FX, bool MASK = false>
 __device__ __forceinline__ void tile_compute(const KParams &p, const unsigned char *stage, const TileInfo &ti,
                                              const ThreadGeom &g, int i0, int j0, int k0, int lane, int warp,
                                              double &acc, unsigned &cnt, unsigned *s_hist, float (&fv)[kTZ],
-                                             const TF *nfp, int nk)
+                                             const TF *nfp, int nk, unsigned mbits = 0xffu)
 {
     static_assert(kTZ % 2 == 0, "voxels are processed in z pairs");
     constexpr unsigned ES = sizeof(TM);
@@ -441,7 +455,9 @@ __device__ __forceinline__ void tile_compute(const KParams &p, const unsigned ch
         const f32x2 val2 = lerp2(wz2, vxx0, vxx1);
         float val0, val1;
         upk(val2, val0, val1);
-        const bool live0 = row_ok && kp < kcnt, live1 = row_ok && kp + 1 < kcnt;
+        const bool live0 = row_ok && kp < kcnt && (!MASK || ((mbits >> kp) & 1u));
+        const bool live1 = row_ok && kp + 1 < kcnt && (!MASK || ((mbits >> (kp + 1)) & 1u));
+        static_assert(!(MASK && STORE), "a masked metric does not store (the mask would punch holes in the output)");
         if (STORE) {
             // one 64-bit output pointer stepped by the plane pitch: 2 address instructions per store, not 5
             const TO o0 = tile_to_out<TO, VTK>(val0), o1 = tile_to_out<TO, VTK>(val1);
@@ -511,6 +527,7 @@ __device__ __noinline__ void tile_compute_nobox(const KParams &p, const double *
             in = sample_voxel<TM, VTK>(mov, p.mov.nx, p.mov.ny, p.mov.nz, r, 0, val);
         }
         if (STORE) out[(size_t)kz * plane] = in ? tile_to_out<TO, VTK>(val) : bgv;
+        if (METRIC != kNone && in && p.fmask && __ldg(p.fmask + gofs + (size_t)kz * plane) == 0) in = false;
         if (METRIC != kNone && in) {
             const float f = (float)__ldg(fixed + (size_t)kz * plane);
             if (METRIC == kSsd) {
@@ -538,7 +555,7 @@ struct TileSmem {
     static size_t bytes(int bins) { return (size_t)kHistOff + sizeof(unsigned) * (size_t)bins * bins; }
 };
 
-template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, class BOX, int NST, int MINB, bool PREFETCH>
+template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, class BOX, int NST, int MINB, bool PREFETCH, bool MASK = false>
 __global__ void __launch_bounds__(kTileThreads, MINB)
 tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ KParams p)
 {
@@ -657,15 +674,24 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ KP
             if (METRIC != kNone && !PREFETCH) nfp = fixed_col(tix, tiy, tiz, nk);
             advance();                                   // (tix, tiy, tiz) is now the NEXT tile
             if (METRIC != kNone && PREFETCH && n + 1 < ntile_mine) nfp = fixed_col(tix, tiy, tiz, nk);
+            unsigned mbits = 0xffu;
+            if (MASK) {
+                const int i = i0 + lane, j = j0 + warp;
+                const int mk = (i < p.ox && j < p.oy) ? min(kTZ, p.oz - k0) : 0;
+                mbits = load_mask_bits(p.fmask + (((size_t)k0 * p.oy + j) * p.ox + i), mk, plane);
+            }
             mbar_wait<32>(bar0 + 8 * s, ph);
             const TileInfo ti = infos[n & 63];
             const unsigned char *stage = tsm + L::kStageBytes * s;
-            if (ti.cls == kInterior) {
-                tile_compute<TM, TF, TO, METRIC, STORE, VTK, false, BOX, PREFETCH ? kFxPrefetchNext : kFxLoadHere>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt, s_hist,
-                                                                         fv, nfp, nk);
+            if (MASK && __all_sync(0xffffffffu, mbits == 0u)) {
+                // nothing of this warp's row is inside the mask: no arithmetic, only keep the prefetch registers moving
+                if (METRIC != kNone && PREFETCH) load_fixed<TF>(fv, nfp, nk, plane);
+            } else if (ti.cls == kInterior) {
+                tile_compute<TM, TF, TO, METRIC, STORE, VTK, false, BOX, PREFETCH ? kFxPrefetchNext : kFxLoadHere, MASK>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt, s_hist,
+                                                                         fv, nfp, nk, mbits);
             } else if (ti.cls == kBorder) {
-                tile_compute<TM, TF, TO, METRIC, STORE, VTK, true, BOX, PREFETCH ? kFxPrefetchNext : kFxLoadHere>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt, s_hist,
-                                                                        fv, nfp, nk);
+                tile_compute<TM, TF, TO, METRIC, STORE, VTK, true, BOX, PREFETCH ? kFxPrefetchNext : kFxLoadHere, MASK>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt, s_hist,
+                                                                        fv, nfp, nk, mbits);
             } else {
                 if (STORE || ti.cls == kNoFit)
                     tile_compute_nobox<TM, TF, TO, METRIC, STORE, VTK>(p, p.dA ? p.dA + 12 * m : p.A0.a, ti.cls, i0, j0, k0, lane, warp,

@@ -37,7 +37,7 @@ struct MultiSmem {
     static constexpr unsigned kBytes = kCntOff + 4u * G * kMaxMulti * kMultiLanes;
 };
 
-template <typename TM, typename TF, bool VTK, class BOX, int NST, int G>
+template <typename TM, typename TF, bool VTK, class BOX, int NST, int G, bool MASK = false>
 __global__ void __launch_bounds__(32 * (kConsumerWarps * G + 1), 1)
 tile_multi_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ KParams p, const int n_mats)
 {
@@ -154,6 +154,19 @@ tile_multi_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constan
                 const TF *fp = static_cast<const TF *>(p.fixed) + (((size_t)k0 * p.oy + j) * p.ox + i);
                 load_fixed<TF>(fv, fp, nk, plane);
             }
+            unsigned mbits = 0xffu;
+            if (MASK) {                                   // the mask of the tile position, shared by every matrix
+                const int i = i0 + lane, j = j0 + warp;
+                const int mk = (i < p.ox && j < p.oy) ? min(kTZ, p.oz - k0) : 0;
+                mbits = load_mask_bits(p.fmask + (((size_t)k0 * p.oy + j) * p.ox + i), mk, plane);
+                if (__all_sync(0xffffffffu, mbits == 0u)) {       // nothing of this warp's row is in the mask
+                    __syncwarp();
+                    mbar_wait<32>(bar0 + 8 * s, ph);
+                    if (lane == 0) mbar_arrive(bar0 + 8 * (NST + s));
+                    if (++s == NST) { s = 0; ph ^= 1u; }
+                    continue;
+                }
+            }
             mbar_wait<32>(bar0 + 8 * s, ph);
             const unsigned char *stage = tsm + L::kStageBytes * s;
             // group (grp + n) mod G starts at matrix 0: with 13 matrices and 2 groups the 7 / 6 split alternates
@@ -168,11 +181,11 @@ tile_multi_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constan
                 } else {
                     const ThreadGeom geom = make_thread_geom(s_A + 12 * m, lane, warp);
                     if (ti.cls == kInterior)
-                        tile_compute<TM, TF, TM, kSsd, false, VTK, false, BOX, kFxKeep>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt,
-                                                                                        nullptr, fv, nullptr, 0);
+                        tile_compute<TM, TF, TM, kSsd, false, VTK, false, BOX, kFxKeep, MASK>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt,
+                                                                                        nullptr, fv, nullptr, 0, mbits);
                     else
-                        tile_compute<TM, TF, TM, kSsd, false, VTK, true, BOX, kFxKeep>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt,
-                                                                                       nullptr, fv, nullptr, 0);
+                        tile_compute<TM, TF, TM, kSsd, false, VTK, true, BOX, kFxKeep, MASK>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt,
+                                                                                       nullptr, fv, nullptr, 0, mbits);
                 }
                 // per-thread accumulators in shared memory: nothing between two tiles waits on another lane
                 g_acc[m * kMultiLanes] += acc;

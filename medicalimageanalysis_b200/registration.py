@@ -37,6 +37,7 @@ class RegistrationConfig:
     frange: tuple | None = None      # intensity ranges for MI; None -> from the volumes, once
     mrange: tuple | None = None
     graph_iters: int = 10            # iterations captured per CUDA graph (0 = no graph)
+    fixed_mask: object = None        # uint8 CUDA tensor on the fixed lattice (SetMetricFixedMask); None = all voxels
 
 
 @dataclass
@@ -135,6 +136,9 @@ def register_rigid(fixed, moving, params0=None, cfg: RegistrationConfig | None =
     ws = kernels.MetricWorkspace(dev, n_mats=N_PROBES, bins=cfg.bins)
     d_A = torch.zeros((N_PROBES, 3, 4), dtype=torch.float64, device=dev)
     state = torch.zeros(int(lib.mia_optimizer_state_bytes()), dtype=torch.uint8, device=dev)
+    fmask = None
+    if cfg.fixed_mask is not None:
+        fmask = kernels._mask_u8(cfg.fixed_mask, fixed.array.shape, dev)      # converted once, outside the loop
     if not is_ssd:
         frange = cfg.frange or _intensity_range(fixed.array)
         mrange = cfg.mrange or _intensity_range(moving.array)
@@ -150,11 +154,11 @@ def register_rigid(fixed, moving, params0=None, cfg: RegistrationConfig | None =
 
         def one_iteration():
             if is_ssd:
-                kernels.resample_ssd(fixed.array, moving.array, d_A=d_A, mode=cfg.mode, ws=ws)
+                kernels.resample_ssd(fixed.array, moving.array, d_A=d_A, mode=cfg.mode, ws=ws, fixed_mask=fmask)
                 metric = ws.ssd
             else:
                 kernels.resample_jointhist(fixed.array, moving.array, frange, mrange, bins=cfg.bins, d_A=d_A,
-                                           mode=cfg.mode, ws=ws)
+                                           mode=cfg.mode, ws=ws, fixed_mask=fmask)
                 kernels.mi_from_hist(ws.hist, out=ws.mi)
                 metric = ws.mi
             _lib.check(lib.mia_optimizer_step(state.data_ptr(), metric.data_ptr(), ws.count.data_ptr(),
@@ -237,7 +241,13 @@ def register_rigid_multires(fixed, moving, params0=None, cfg: RegistrationConfig
     for f, n_it in zip(levels, iters):
         fl, ml = pyramid_level(fixed, f), pyramid_level(moving, f)
         gi = cfg.graph_iters if n_it >= cfg.graph_iters else 0
-        lcfg = dataclasses.replace(cfg, iterations=int(n_it), frange=frange, mrange=mrange, graph_iters=gi)
+        lmask = None
+        if cfg.fixed_mask is not None:               # a coarse voxel is inside when at least half of its block is
+            from . import kernels
+            m8 = kernels._mask_u8(cfg.fixed_mask, fixed.array.shape, fixed.array.device)
+            lmask = m8 if f == (1, 1, 1) else (kernels.shrink_mean((m8 != 0).float(), f) >= 0.5).to(m8.dtype)
+        lcfg = dataclasses.replace(cfg, iterations=int(n_it), frange=frange, mrange=mrange, graph_iters=gi,
+                                   fixed_mask=lmask)
         res = register_rigid(fl, ml, params0=params, cfg=lcfg, center=center)
         params = res.params
         evals += res.evaluations

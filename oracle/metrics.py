@@ -30,21 +30,26 @@ def bin_index(v, vmin, vmax, bins):
     return np.clip(b, 0, bins - 1).astype(np.int64)
 
 
-def oracle_ssd(fixed, mov, A, mode="itk"):
-    """(ssd float64, n_valid int).  ``fixed`` defines the output lattice ([z,y,x])."""
+def oracle_ssd(fixed, mov, A, mode="itk", fixed_mask=None):
+    """(ssd float64, n_valid int).  ``fixed`` defines the output lattice ([z,y,x]); ``fixed_mask`` (same lattice):
+    voxels where it is 0 take no part (SetMetricFixedMask, ``utils/deformable/simpleitk.py:116-117``)."""
     fixed = np.asarray(fixed)
     odims = (fixed.shape[2], fixed.shape[1], fixed.shape[0])
     _, vals, mask = oracle_reslice(mov, A, odims, 0.0, mode, np.float32, return_float=True)
+    if fixed_mask is not None:
+        mask = mask & (np.asarray(fixed_mask) > 0)
     d = fixed.astype(np.float64) - vals
     d = d[mask]
     return float(np.sum(d * d)), int(mask.sum())
 
 
-def oracle_joint_hist(fixed, mov, A, bins, frange, mrange, mode="itk"):
+def oracle_joint_hist(fixed, mov, A, bins, frange, mrange, mode="itk", fixed_mask=None):
     """(H uint64 [bins, bins] indexed [fixed_bin, moving_bin], n_valid)."""
     fixed = np.asarray(fixed)
     odims = (fixed.shape[2], fixed.shape[1], fixed.shape[0])
     _, vals, mask = oracle_reslice(mov, A, odims, 0.0, mode, np.float32, return_float=True)
+    if fixed_mask is not None:
+        mask = mask & (np.asarray(fixed_mask) > 0)
     bf = bin_index(fixed[mask], frange[0], frange[1], bins)
     bm = bin_index(vals[mask].astype(np.float32), mrange[0], mrange[1], bins)
     H = np.bincount(bf * bins + bm, minlength=bins * bins).reshape(bins, bins).astype(np.uint64)
