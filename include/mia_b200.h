@@ -231,6 +231,21 @@ int mia_resample_jointhist_masked(const void *d_mov, int mov_dtype, const int md
                                   float mmax, int bins, unsigned int *d_hist, unsigned long long *d_count, void *d_ws,
                                   size_t ws_bytes, void *stream);
 
+/*
+ * SURVEY N5 -- Mattes mutual information ("AdvancedMattesMutualInformation" + NumberOfHistogramBins,
+ * utils/deformable/simpleitk.py:155-156; itk::MattesMutualInformationImageToImageMetricv4): `bins` bins per axis of
+ * which 2 on either side are padding, box window on the fixed image, cubic B-spline Parzen window over 4 bins on
+ * the moving image.  The B-spline is evaluated on a 1/256 sub-bin lattice with integer weights that sum to 1024 per
+ * sample, so d_hist ([n][bins][bins] uint64, units of 1/1024 sample) is an INTEGER histogram: bit-identical for
+ * every grid, sharding and GPU count; d_count[n] = samples.  mia_mi_from_hist64 turns it into MI (nats).
+ * d_fixed_mask may be NULL.
+ */
+int mia_resample_mattes(const void *d_mov, int mov_dtype, const int mdims[3], const void *d_fixed, int fixed_dtype,
+                        const unsigned char *d_fixed_mask, const int odims[3], int n_mats, const double *A,
+                        const double *d_A, int mode, float fmin, float fmax, float mmin, float mmax, int bins,
+                        unsigned long long *d_hist, unsigned long long *d_count, void *d_ws, size_t ws_bytes, void *stream);
+int mia_mi_from_hist64(const unsigned long long *d_hist, int bins, int n_mats, double *d_mi, void *stream);
+
 /* Page-locked host buffers for the *_host entry point (a NumPy array can wrap them). */
 void *mia_host_alloc(size_t bytes);
 int mia_host_free(void *p);

@@ -176,6 +176,16 @@ template <> struct TileCfg<int16_t, kHist> : TileCfgT<MIA_CFG_I16_HIST> {};
 template <> struct TileCfg<float, kNone> : TileCfgT<MIA_CFG_F32_STORE> {};
 template <> struct TileCfg<float, kSsd> : TileCfgT<MIA_CFG_F32_SSD> {};
 template <> struct TileCfg<float, kHist> : TileCfgT<MIA_CFG_F32_HIST> {};
+template <> struct TileCfg<int16_t, kMattes> : TileCfgT<MIA_CFG_I16_HIST> {};   // same shared-memory budget as the hard-binned histogram
+template <> struct TileCfg<float, kMattes> : TileCfgT<MIA_CFG_F32_HIST> {};
+
+// Mattes counters are 32-bit per CTA in units of 1 / 1024 sample: a CTA may see at most 2^22 voxels (2^21 kept as the
+// limit), so large lattices get more blocks than are resident.
+long long mattes_min_grid(const KParams &p)
+{
+    const long long nvox = (long long)p.ox * p.oy * p.oz;
+    return (nvox + (1LL << 21) - 1) >> 21;
+}
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
@@ -249,7 +259,7 @@ int launch_tile(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream
     constexpr int NST = CFG::NST, MINB = CFG::MINB;
     constexpr bool PREFETCH = CFG::PREFETCH;
     auto k = tile_kernel<TM, TF, TO, METRIC, STORE, VTK, BOX, NST, MINB, PREFETCH, MASK>;
-    const size_t smem = TileSmem<TM, BOX, NST>::bytes(METRIC == kHist ? p.bins : 0);
+    const size_t smem = TileSmem<TM, BOX, NST>::bytes((METRIC == kHist || METRIC == kMattes) ? p.bins : 0, METRIC == kMattes);
     static std::mutex mu;
     static std::map<std::pair<int, size_t>, int> occ;     // (device, smem) -> resident CTAs per SM
     static std::map<int, size_t> attr;                    // device -> dynamic shared memory the kernel is allowed
@@ -274,6 +284,7 @@ int launch_tile(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream
         }
     }
     long long gx = (long long)sm_count() * nb;
+    if (METRIC == kMattes && gx < mattes_min_grid(p)) gx = mattes_min_grid(p);
     if (gx > p.ntiles) gx = p.ntiles;
     if (gx > kMaxGridX) gx = kMaxGridX;
     dim3 grid((unsigned)gx, (unsigned)n_mats, 1);
@@ -606,7 +617,56 @@ int mia_mi_from_hist(const unsigned int *d_hist, int bins, int n_mats, double *d
     if (!d_hist || !d_mi) return fail(MIA_ERR_ARG, "mia_mi_from_hist: null pointer");
     if (bins < 2 || bins > MIA_MAX_BINS || n_mats < 1) return fail(MIA_ERR_ARG, "mia_mi_from_hist: bad bins / n_mats");
     const size_t smem = sizeof(double) * (2 * (size_t)bins + 256);
-    mi_kernel<<<n_mats, 256, smem, (cudaStream_t)stream>>>(d_hist, bins, d_mi);
+    mi_kernel<unsigned><<<n_mats, 256, smem, (cudaStream_t)stream>>>(d_hist, bins, d_mi);
+    CUDA_TRY(cudaGetLastError());
+    return MIA_OK;
+}
+
+int mia_mi_from_hist64(const unsigned long long *d_hist, int bins, int n_mats, double *d_mi, void *stream)
+{
+    if (!d_hist || !d_mi) return fail(MIA_ERR_ARG, "mia_mi_from_hist64: null pointer");
+    if (bins < 2 || bins > MIA_MAX_BINS || n_mats < 1) return fail(MIA_ERR_ARG, "mia_mi_from_hist64: bad bins / n_mats");
+    const size_t smem = sizeof(double) * (2 * (size_t)bins + 256);
+    mi_kernel<unsigned long long><<<n_mats, 256, smem, (cudaStream_t)stream>>>(d_hist, bins, d_mi);
+    CUDA_TRY(cudaGetLastError());
+    return MIA_OK;
+}
+
+int mia_resample_mattes(const void *d_mov, int mov_dtype, const int mdims[3], const void *d_fixed, int fixed_dtype,
+                        const unsigned char *d_fixed_mask, const int odims[3], int n_mats, const double *A,
+                        const double *d_A, int mode, float fmin, float fmax, float mmin, float mmax, int bins,
+                        unsigned long long *d_hist, unsigned long long *d_count, void *d_ws, size_t ws_bytes, void *stream)
+{
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!d_hist || !d_count) return fail(MIA_ERR_ARG, "mia_resample_mattes: null result pointer");
+    if (bins < 8 || bins > MIA_MAX_BINS) return fail(MIA_ERR_ARG, "mia_resample_mattes: bins must be 8..%d (4 of them are padding)", MIA_MAX_BINS);
+    if (!(fmax > fmin) || !(mmax > mmin)) return fail(MIA_ERR_ARG, "mia_resample_mattes: empty intensity range");
+    KParams p;
+    WsLayout w;
+    int rc = metric_common(p, "mia_resample_mattes", d_mov, mov_dtype, mdims, d_fixed, fixed_dtype, odims, n_mats, A, d_A,
+                           mode, d_ws, ws_bytes, s, w);
+    if (rc) return rc;
+    p.fmask = d_fixed_mask;
+    p.d_hist64 = d_hist;
+    p.d_count = d_count;
+    p.bins = bins;
+    p.fmin = fmin; p.fscale = (float)(bins - 4) / (fmax - fmin);
+    p.mmin = mmin; p.mscale = (float)(bins - 4) / (mmax - mmin);
+    if (mattes_min_grid(p) > kMaxGridX) return fail(MIA_ERR_UNSUPPORTED, "mia_resample_mattes: lattice too large for 32-bit block counters");
+    CUDA_TRY(cudaMemsetAsync(d_hist, 0, sizeof(unsigned long long) * (size_t)n_mats * bins * bins, s));
+    const size_t smem = sizeof(unsigned) * (size_t)bins * bins + 8u * (kParzenSteps + 1) + 8u;
+    long long gx = (long long)sm_count() * (smem > 32 * 1024 ? 2 : 4);
+    if (gx < mattes_min_grid(p)) gx = mattes_min_grid(p);
+    if (gx > p.ntiles) gx = p.ntiles;
+    if (gx > kMaxGridX) gx = kMaxGridX;
+    dim3 grid((unsigned)gx, (unsigned)n_mats, 1);
+    g_last_path = 0;
+    if (mov_dtype == fixed_dtype) {
+        bool launched = false;
+        const int trc = try_tile<kMattes, false>(mov_dtype, mode, d_mov, mdims, d_A ? nullptr : A, n_mats, p, s, launched);
+        if (launched) return trc;
+    }
+    dispatch_metric<kMattes, false>(mov_dtype, fixed_dtype, p, mode, grid, smem, s);
     CUDA_TRY(cudaGetLastError());
     return MIA_OK;
 }

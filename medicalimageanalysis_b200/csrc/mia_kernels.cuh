@@ -4,7 +4,7 @@
 
 namespace mia {
 
-enum Metric { kNone = 0, kSsd = 1, kHist = 2 };
+enum Metric { kNone = 0, kSsd = 1, kHist = 2, kMattes = 3 };
 
 struct KParams {
     VolView mov;                 // moving volume
@@ -26,6 +26,7 @@ struct KParams {
     double *d_ssd;               // [n_mats]
     unsigned long long *d_count; // [n_mats]
     unsigned *d_hist;            // [n_mats][bins][bins]
+    unsigned long long *d_hist64; // kMattes: [n_mats][bins][bins] in units of 1 / kParzenOne sample
     float fmin, fscale, mmin, mscale;
     int bins;
 };
@@ -40,6 +41,49 @@ __device__ __forceinline__ int bin_of(float v, float vmin, float scale, int bins
     float b = floorf((v - vmin) * scale);
     b = fminf(fmaxf(b, 0.0f), (float)(bins - 1));   // NaN -> 0 via fmaxf
     return (int)b;
+}
+
+// ---- Mattes mutual information: Parzen-window joint histogram ------------------------------------------
+// Structure of itk::MattesMutualInformationImageToImageMetricv4 (what "AdvancedMattesMutualInformation" +
+// NumberOfHistogramBins ask of Elastix, utils/deformable/simpleitk.py:155-156): B bins with 2 padding bins on either
+// side, a zero-order (box) window on the fixed image and a cubic B-spline window over 4 bins on the moving image.
+// To keep the histogram an INTEGER one (order-independent, bit-identical for any grid, sharding or GPU count) the
+// B-spline is evaluated on a 1/256 sub-bin lattice with 10-bit weights that sum to kParzenOne exactly; the table is
+// built with integer arithmetic only, so host oracle and device agree bit for bit.
+constexpr int kParzenOne = 1024, kParzenSteps = 256;
+
+__host__ __device__ inline void parzen_weights(int k, unsigned short q[4])
+{
+    // t = k / 256;  w0 = (1-t)^3 / 6, w1 = (4 - 6 t^2 + 3 t^3) / 6, w3 = t^3 / 6, w2 = the rest; q = round(1024 w)
+    const long long T = kParzenSteps, T3 = T * T * T, den = 6 * T3, one = kParzenOne;
+    const long long a = T - k;
+    const long long n0 = a * a * a, n1 = 4 * T3 - 6 * (long long)k * k * T + 3 * (long long)k * k * k, n3 = (long long)k * k * k;
+    const long long q0 = (2 * one * n0 + den) / (2 * den), q1 = (2 * one * n1 + den) / (2 * den), q3 = (2 * one * n3 + den) / (2 * den);
+    q[0] = (unsigned short)q0; q[1] = (unsigned short)q1; q[3] = (unsigned short)q3;
+    q[2] = (unsigned short)(one - q0 - q1 - q3);
+}
+
+// lut: [kParzenSteps + 1][4] unsigned short in shared memory, right behind the bins * bins counters
+__device__ __forceinline__ void parzen_lut_fill(unsigned short *lut, int tid, int nthreads)
+{
+    for (int k = tid; k <= kParzenSteps; k += nthreads) parzen_weights(k, lut + 4 * k);
+}
+
+// One sample into the CTA's histogram.  p.fscale / p.mscale are (bins - 4) / range here.
+__device__ __forceinline__ void mattes_add(unsigned *s_hist, const unsigned short *lut, float f, float v, float fmin,
+                                           float fscale, float mmin, float mscale, int bins)
+{
+    const int fb = bin_of(f, fmin, fscale, bins - 4) + 2;
+    float b = fmaxf((v - mmin) * mscale, 0.0f);                       // NaN -> 0 like bin_of
+    const float i0 = fminf(floorf(b), (float)(bins - 5));
+    const float t = fminf(b - i0, 1.0f);
+    const int tq = (int)floorf(fmaf(t, (float)kParzenSteps, 0.5f));
+    const ushort4 w = *reinterpret_cast<const ushort4 *>(lut + 4 * tq);
+    unsigned *cell = s_hist + fb * bins + (int)i0 + 1;                // first Parzen bin = (i0 + 2) - 1
+    if (w.x) atomicAdd(cell, (unsigned)w.x);
+    atomicAdd(cell + 1, (unsigned)w.y);
+    atomicAdd(cell + 2, (unsigned)w.z);
+    if (w.w) atomicAdd(cell + 3, (unsigned)w.w);
 }
 
 // One launch does everything: grid.x blocks stride over the (x-tile, y-tile, z) tiles of the output
@@ -61,8 +105,10 @@ __global__ void __launch_bounds__(kThreads) resample_kernel(const KParams p)
     const int tx = threadIdx.x, ty = threadIdx.y;
     const int tid = ty * kBlockX + tx;
 
-    if (METRIC == kHist) {
+    unsigned short *s_lut = reinterpret_cast<unsigned short *>(s_hist + p.bins * p.bins);
+    if (METRIC == kHist || METRIC == kMattes) {
         for (int b = tid; b < p.bins * p.bins; b += kThreads) s_hist[b] = 0u;
+        if (METRIC == kMattes) parzen_lut_fill(s_lut, tid, kThreads);
         __syncthreads();
     }
 
@@ -123,6 +169,10 @@ __global__ void __launch_bounds__(kThreads) resample_kernel(const KParams p)
                 atomicAdd(&s_hist[bf * p.bins + bm], 1u);
                 ++cnt;
             }
+            if (METRIC == kMattes && in) {
+                mattes_add(s_hist, s_lut, fv[v], val, p.fmin, p.fscale, p.mmin, p.mscale, p.bins);
+                ++cnt;
+            }
         }
         if (METRIC == kSsd) acc += (double)part;
         if (STORE) {
@@ -158,6 +208,13 @@ __global__ void __launch_bounds__(kThreads) resample_kernel(const KParams p)
         for (int b = tid; b < p.bins * p.bins; b += kThreads) {
             const unsigned c = s_hist[b];
             if (c) atomicAdd(gh + b, c);
+        }
+    }
+    if (METRIC == kMattes) {
+        unsigned long long *gh = p.d_hist64 + (size_t)m * p.bins * p.bins;
+        for (int b = tid; b < p.bins * p.bins; b += kThreads) {
+            const unsigned c = s_hist[b];
+            if (c) atomicAdd(gh + b, (unsigned long long)c);
         }
     }
 
@@ -206,11 +263,12 @@ __global__ void __launch_bounds__(kThreads) resample_kernel(const KParams p)
 
 // ---------------------------------------------------------------------------------------------
 // MI from an integer joint histogram: one block per matrix, float64, fixed-order tree reductions.
-__global__ void __launch_bounds__(256) mi_kernel(const unsigned *__restrict__ hist, int bins, double *mi)
+template <typename CT>
+__global__ void __launch_bounds__(256) mi_kernel(const CT *__restrict__ hist, int bins, double *mi)
 {
     extern __shared__ double s_buf[];        // [bins] row sums, [bins] col sums, [256] scratch
     double *rowsum = s_buf, *colsum = s_buf + bins, *red = s_buf + 2 * bins;
-    const unsigned *h = hist + (size_t)blockIdx.x * bins * bins;
+    const CT *h = hist + (size_t)blockIdx.x * bins * bins;
     const int tid = threadIdx.x;
     for (int b = tid; b < bins; b += 256) {
         double rs = 0.0, cs = 0.0;
@@ -235,7 +293,7 @@ __global__ void __launch_bounds__(256) mi_kernel(const unsigned *__restrict__ hi
     part = 0.0;
     if (n > 0.0) {
         for (int e = tid; e < bins * bins; e += 256) {
-            const unsigned c = h[e];
+            const CT c = h[e];
             if (c) {
                 const double hc = (double)c;
                 part += (hc / n) * log(hc * n / (rowsum[e / bins] * colsum[e % bins]));

@@ -487,6 +487,12 @@ __device__ __forceinline__ void tile_compute(const KParams &p, const unsigned ch
             if (live0 && in0) red_shared_inc(h0);
             if (live1 && in1) red_shared_inc(h1);
         }
+        if (METRIC == kMattes) {
+            // Parzen-window joint histogram (mattes_add, mia_kernels.cuh); the voxel count is the histogram sum / 1024
+            const unsigned short *lut = reinterpret_cast<const unsigned short *>(s_hist + p.bins * p.bins);
+            if (live0 && in0) mattes_add(s_hist, lut, fv[kp], val0, p.fmin, p.fscale, p.mmin, p.mscale, p.bins);
+            if (live1 && in1) mattes_add(s_hist, lut, fv[kp + 1], val1, p.fmin, p.fscale, p.mmin, p.mscale, p.bins);
+        }
         if (METRIC != kNone && FX == kFxPrefetchNext) {
             asm("" : "+l"(nfp));                     // keep ONE stepped 64-bit pointer (2 instructions per load)
             fv[kp] = kp < nk ? (float)__ldg(nfp) : 0.0f;
@@ -533,6 +539,9 @@ __device__ __noinline__ void tile_compute_nobox(const KParams &p, const double *
             if (METRIC == kSsd) {
                 const float d = f - val;
                 part = fmaf(d, d, part);
+            } else if (METRIC == kMattes) {
+                mattes_add(s_hist, reinterpret_cast<const unsigned short *>(s_hist + p.bins * p.bins), f, val, p.fmin, p.fscale,
+                           p.mmin, p.mscale, p.bins);
             } else {
                 atomicAdd(&s_hist[bin_of(f, p.fmin, p.fscale, p.bins) * p.bins + bin_of(val, p.mmin, p.mscale, p.bins)], 1u);
             }
@@ -552,7 +561,11 @@ struct TileSmem {
     static constexpr unsigned kBarOff = kStageBytes * NST;
     static constexpr unsigned kInfoOff = kBarOff + 16u * NST;
     static constexpr unsigned kHistOff = (kInfoOff + (unsigned)sizeof(TileInfo) * 64u + 15u) & ~15u;
-    static size_t bytes(int bins) { return (size_t)kHistOff + sizeof(unsigned) * (size_t)bins * bins; }
+    // the Parzen table of the Mattes kernels ([257][4] unsigned short) sits right behind the counters
+    static size_t bytes(int bins, bool parzen = false)
+    {
+        return (size_t)kHistOff + sizeof(unsigned) * (size_t)bins * bins + (parzen ? 8u * (kParzenSteps + 1) + 8u : 0u);
+    }
 };
 
 template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, class BOX, int NST, int MINB, bool PREFETCH, bool MASK = false>
@@ -585,8 +598,9 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ KP
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (METRIC == kHist)
+    if (METRIC == kHist || METRIC == kMattes)
         for (int b = tid; b < p.bins * p.bins; b += kTileThreads) s_hist[b] = 0u;
+    if (METRIC == kMattes) parzen_lut_fill(reinterpret_cast<unsigned short *>(s_hist + p.bins * p.bins), tid, kTileThreads);
     __syncthreads();
 
     double acc = 0.0;
@@ -722,10 +736,25 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ KP
             cnt += c;
         }
     }
+    unsigned long long wsum = 0;
+    if (METRIC == kMattes) {
+        // 64-bit global counters; every sample added kParzenOne in total, so the voxel count is the sum / kParzenOne
+        // (taken per block: the host sizes the grid so that a block's sum stays below 2^32 * 2^10)
+        __syncthreads();
+        unsigned long long *gh = p.d_hist64 + (size_t)m * p.bins * p.bins;
+        for (int b = tid; b < p.bins * p.bins; b += kTileThreads) {
+            const unsigned c = s_hist[b];
+            if (c) atomicAdd(gh + b, (unsigned long long)c);
+            wsum += c;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, o);
+        cnt = 0;
+    }
     cnt = warp_sum_u(cnt);
     if (lane == 0) {
         s_red[warp] = acc;
-        s_redc[warp] = cnt;
+        s_redc[warp] = METRIC == kMattes ? wsum : (unsigned long long)cnt;
     }
     __syncthreads();
     if (tid == 0) {
@@ -735,6 +764,7 @@ tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ KP
             sacc += s_red[w];
             c += s_redc[w];
         }
+        if (METRIC == kMattes) c /= (unsigned long long)kParzenOne;
         p.ws_ssd[(size_t)m * gridDim.x + blockIdx.x] = sacc;
         p.ws_cnt[(size_t)m * gridDim.x + blockIdx.x] = (unsigned)c;
         __threadfence();

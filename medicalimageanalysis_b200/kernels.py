@@ -133,6 +133,14 @@ class MetricWorkspace:
         self.count = torch.zeros(self.n_mats, dtype=torch.int64, device=self.device)
         self.hist = torch.zeros((self.n_mats, self.bins, self.bins), dtype=torch.int32, device=self.device)
         self.mi = torch.zeros(self.n_mats, dtype=torch.float64, device=self.device)
+        self._hist64 = None
+
+    @property
+    def hist64(self):
+        """[n_mats, bins, bins] int64 counters of the Mattes (Parzen) histogram, allocated on first use."""
+        if self._hist64 is None:
+            self._hist64 = torch.zeros((self.n_mats, self.bins, self.bins), dtype=torch.int64, device=self.device)
+        return self._hist64
 
 
 def _A_args(A, d_A, n_expected=None):
@@ -192,8 +200,27 @@ def resample_jointhist(fixed, mov, frange, mrange, bins=64, A=None, d_A=None, mo
     return ws.hist[:n], ws.count[:n]
 
 
+def resample_mattes(fixed, mov, frange, mrange, bins=50, A=None, d_A=None, mode="itk", ws=None, fixed_mask=None):
+    """Fused resample + Mattes (Parzen-window) joint histogram.  Returns (hist[n, bins, bins] int64 in
+    units of 1/1024 sample, count[n] i64) device tensors; ``mi_from_hist`` turns the histogram into MI."""
+    lib = _lib.load()
+    fixed, mov = _vol(fixed, "fixed"), _vol(mov, "mov")
+    n, Ah, Ad = _A_args(A, d_A)
+    if ws is None or ws.n_mats < n or ws.bins != bins:
+        ws = MetricWorkspace(mov.device, n_mats=n, bins=bins)
+    fm = _fixed_mask(fixed_mask, fixed)
+    with torch.cuda.device(mov.device):
+        check(lib.mia_resample_mattes(mov.data_ptr(), _DT[mov.dtype], _dims(mov), fixed.data_ptr(), _DT[fixed.dtype],
+                                      fm.data_ptr() if fm is not None else None, _dims(fixed), n, Ah, Ad, _MODE[mode],
+                                      float(frange[0]), float(frange[1]), float(mrange[0]), float(mrange[1]), int(bins),
+                                      ws.hist64.data_ptr(), ws.count.data_ptr(), ws.ws.data_ptr(), ws.ws.numel(),
+                                      _stream(mov)))
+    return ws.hist64[:n], ws.count[:n]
+
+
 def mi_from_hist(hist, out=None):
-    """MI (nats, float64) of each ``[bins, bins]`` integer histogram in ``hist`` ([n, bins, bins] int32)."""
+    """MI (nats, float64) of each ``[bins, bins]`` integer histogram in ``hist`` ([n, bins, bins] int32, or int64 for
+    the Mattes histogram)."""
     lib = _lib.load()
     if hist.dim() == 2:
         hist = hist[None]
@@ -201,8 +228,9 @@ def mi_from_hist(hist, out=None):
     n, bins = hist.shape[0], hist.shape[1]
     if out is None:
         out = torch.empty(n, dtype=torch.float64, device=hist.device)
+    fn = lib.mia_mi_from_hist64 if hist.dtype == torch.int64 else lib.mia_mi_from_hist
     with torch.cuda.device(hist.device):
-        check(lib.mia_mi_from_hist(hist.data_ptr(), bins, n, out.data_ptr(), _stream(hist)))
+        check(fn(hist.data_ptr(), bins, n, out.data_ptr(), _stream(hist)))
     return out
 
 

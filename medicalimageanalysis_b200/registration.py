@@ -27,7 +27,8 @@ N_PROBES = 13
 
 @dataclass
 class RegistrationConfig:
-    metric: str = "ssd"              # 'ssd' (mean squares, minimised) or 'mi' (joint-histogram MI, maximised)
+    metric: str = "ssd"              # 'ssd' (mean squares, minimised), 'mi' (hard-binned joint-histogram MI) or
+                                     # 'mattes' (Parzen-window MI); both MI flavours are maximised
     iterations: int = 200
     rot_step_deg: float = 0.5        # probe offset and step length per unit scale, rotations
     trans_step_mm: float = 0.5       # same, translations
@@ -131,8 +132,8 @@ def register_rigid(fixed, moving, params0=None, cfg: RegistrationConfig | None =
     p2w = G.index_to_physical(fixed.grid, "itk")
     w2p = G.physical_to_index(moving.grid, "itk")
     is_ssd = cfg.metric == "ssd"
-    if cfg.metric not in ("ssd", "mi"):
-        raise ValueError("metric must be 'ssd' or 'mi'")
+    if cfg.metric not in ("ssd", "mi", "mattes"):
+        raise ValueError("metric must be 'ssd', 'mi' or 'mattes'")
     ws = kernels.MetricWorkspace(dev, n_mats=N_PROBES, bins=cfg.bins)
     d_A = torch.zeros((N_PROBES, 3, 4), dtype=torch.float64, device=dev)
     state = torch.zeros(int(lib.mia_optimizer_state_bytes()), dtype=torch.uint8, device=dev)
@@ -164,6 +165,17 @@ def register_rigid(fixed, moving, params0=None, cfg: RegistrationConfig | None =
             _lib.check(lib.mia_optimizer_step(state.data_ptr(), metric.data_ptr(), ws.count.data_ptr(),
                                               1 if is_ssd else 0, d_A.data_ptr(), stream()))
 
+        def one_iteration_mattes():
+            kernels.resample_mattes(fixed.array, moving.array, frange, mrange, bins=cfg.bins, d_A=d_A, mode=cfg.mode,
+                                    ws=ws, fixed_mask=fmask)
+            kernels.mi_from_hist(ws.hist64, out=ws.mi)
+            metric = ws.mi
+            _lib.check(lib.mia_optimizer_step(state.data_ptr(), metric.data_ptr(), ws.count.data_ptr(),
+                                              1 if is_ssd else 0, d_A.data_ptr(), stream()))
+
+        if cfg.metric == "mattes":
+            ws.hist64                                 # allocate outside any graph capture
+            one_iteration = one_iteration_mattes
         done = 0
         gi = int(cfg.graph_iters)
         if gi > 0 and cfg.iterations >= gi:
@@ -234,8 +246,8 @@ def register_rigid_multires(fixed, moving, params0=None, cfg: RegistrationConfig
     iters = [cfg.iterations] * len(levels) if iterations is None else list(iterations)
     if len(iters) != len(levels):
         raise ValueError("iterations must have one entry per level")
-    frange = cfg.frange or (_intensity_range(fixed.array) if cfg.metric == "mi" else None)
-    mrange = cfg.mrange or (_intensity_range(moving.array) if cfg.metric == "mi" else None)
+    frange = cfg.frange or (_intensity_range(fixed.array) if cfg.metric != "ssd" else None)
+    mrange = cfg.mrange or (_intensity_range(moving.array) if cfg.metric != "ssd" else None)
     params = np.zeros(6) if params0 is None else np.asarray(params0, dtype=np.float64)
     per_level, evals, res = [], 0, None
     for f, n_it in zip(levels, iters):

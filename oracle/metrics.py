@@ -67,3 +67,45 @@ def oracle_mi(H):
     nzf, nzm = np.nonzero(H)
     h = H[nzf, nzm]
     return float(np.sum((h / n) * np.log(h * n / (pf[nzf] * pm[nzm]))))
+
+
+# ---- Mattes (Parzen-window) mutual information, SURVEY N5 ---------------------------------------------------------
+PARZEN_ONE, PARZEN_STEPS = 1024, 256
+
+
+def parzen_table():
+    """[257, 4] integer weights of the cubic B-spline window on a 1/256 sub-bin lattice, each row summing to 1024.
+    Integer arithmetic only (round half up of 1024 * w): w0 = (1-t)^3/6, w1 = (4 - 6t^2 + 3t^3)/6, w3 = t^3/6."""
+    T = PARZEN_STEPS
+    den = 6 * T ** 3
+    tab = np.zeros((T + 1, 4), dtype=np.int64)
+    for k in range(T + 1):
+        n0, n1, n3 = (T - k) ** 3, 4 * T ** 3 - 6 * k * k * T + 3 * k ** 3, k ** 3
+        q0, q1, q3 = ((2 * PARZEN_ONE * n + den) // (2 * den) for n in (n0, n1, n3))
+        tab[k] = (q0, q1, PARZEN_ONE - q0 - q1 - q3, q3)
+    return tab
+
+
+def oracle_mattes_hist(fixed, mov, A, bins, frange, mrange, mode="itk", fixed_mask=None):
+    """(H uint64 [bins, bins] in units of 1/1024 sample, n_valid).  Structure of
+    itk::MattesMutualInformationImageToImageMetricv4 (named at ``utils/deformable/simpleitk.py:155-156``): 2 padding
+    bins per side, box window on the fixed image, cubic B-spline over 4 bins on the moving image; the spec of the
+    integer quantisation is this repository's (``csrc/mia_kernels.cuh::mattes_add``).  PARITY UNPINNED."""
+    fixed = np.asarray(fixed)
+    odims = (fixed.shape[2], fixed.shape[1], fixed.shape[0])
+    _, vals, mask = oracle_reslice(mov, A, odims, 0.0, mode, np.float32, return_float=True)
+    if fixed_mask is not None:
+        mask = mask & (np.asarray(fixed_mask) > 0)
+    fb = bin_index(fixed[mask], frange[0], frange[1], bins - 4) + 2
+    v = vals[mask].astype(np.float32)
+    mscale = np.float32(bins - 4) / (np.float32(mrange[1]) - np.float32(mrange[0]))
+    b = np.maximum((v - np.float32(mrange[0])) * mscale, np.float32(0))
+    i0 = np.minimum(np.floor(b), np.float32(bins - 5))
+    t = np.minimum(b - i0, np.float32(1))
+    tq = np.floor(t * np.float32(PARZEN_STEPS) + np.float32(0.5)).astype(np.int64)
+    tab = parzen_table()
+    H = np.zeros(bins * bins, dtype=np.int64)
+    base = fb * bins + i0.astype(np.int64) + 1
+    for k in range(4):
+        H += np.bincount(base + k, weights=tab[tq, k], minlength=bins * bins).astype(np.int64)
+    return H.reshape(bins, bins).astype(np.uint64), int(mask.sum())
