@@ -14,6 +14,7 @@
 // row structure to exploit) and split into an integer base + float32 fraction, as make_row_ctx does.
 #pragma once
 #include "mia_device.cuh"
+#include "mia_tile.cuh"
 
 namespace mia {
 
@@ -26,6 +27,7 @@ struct DvfParams {
     double B[9];                 // physical displacement -> moving index displacement (row-major 3x3)
     float background;
     int round_mode;
+    unsigned magic_fold;         // staged kernel: see tile_compute (mia_tile.cuh)
 };
 
 __device__ __forceinline__ RowCtx make_point_ctx(double cx, double cy, double cz, int nx, int ny, int nz)
@@ -104,6 +106,203 @@ __global__ void __launch_bounds__(kDvfThreads, MIA_DVF_MINB) warp_dvf_kernel(con
                 out[v + (size_t)kz * plane] = in ? to_out<TO>(val, p.round_mode) : bg;
             }
         }
+    }
+}
+
+
+// ---------------------------------------------------------------------------------------------------------------
+// Box-staged DVF warp.  A deformation field from a registration is smooth: inside one 32 x 8 x 8 output tile the
+// displaced coordinates stay within a few voxels of the rigid ones, so the tile's taps fit a shared-memory box like
+// the rigid tile kernel's -- only the box is not known before the field has been read.  Per tile a CTA therefore
+// (1) loads its 2048 displacement vectors (lane = x: 384 contiguous bytes per warp and plane) and forms the local
+// coordinates, (2) reduces the integer bounding box of the INSIDE voxels' taps over the CTA (REDUX + 8 shared
+// slots), (3) has one thread fetch that box with one TMA copy (zero fill outside the volume = the edge clamp),
+// (4) computes from shared memory with the packed arithmetic of tile_compute.  A tile whose taps do not fit the box
+// (a tear in the field) takes the per-voxel gather of warp_dvf_kernel, so any field stays correct.  The phases of
+// one CTA are serial; 3-4 resident CTAs per SM overlap them.
+#ifndef MIA_DVF_STAGED_MINB
+#define MIA_DVF_STAGED_MINB 3
+#endif
+template <typename TM, typename TO, bool CLOSED, class BOX>
+__global__ void __launch_bounds__(kDvfThreads, MIA_DVF_STAGED_MINB)
+warp_dvf_tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ DvfParams p)
+{
+    constexpr unsigned ES = sizeof(TM);
+    constexpr int PY = BOX::kX * ES, PZ = BOX::kX * BOX::kY * ES;
+    constexpr int xalign = 16 / (int)sizeof(TM);
+    constexpr unsigned kBoxBytes = BOX::kX * BOX::kY * BOX::kZ * ES;
+    extern __shared__ __align__(1024) unsigned char dsm[];
+    __shared__ int s_box[8][6];
+    __shared__ __align__(8) unsigned long long s_bar;
+
+    const TM *__restrict__ mov = static_cast<const TM *>(p.mov.p);
+    TO *__restrict__ out = static_cast<TO *>(p.out);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ntx = (p.ox + 31) / 32, nty = (p.oy + 7) / 8, ntz = (p.oz + kTZ - 1) / kTZ;
+    const unsigned ntiles = (unsigned)ntx * nty * ntz;
+    const TO bg = tile_to_out<TO, CLOSED>(p.background);
+    const double *A = p.A.a;
+    const float a2x = (float)A[2], a2y = (float)A[6], a2z = (float)A[10];
+    const float b00 = (float)p.B[0], b01 = (float)p.B[1], b02 = (float)p.B[2];
+    const float b10 = (float)p.B[3], b11 = (float)p.B[4], b12 = (float)p.B[5];
+    const float b20 = (float)p.B[6], b21 = (float)p.B[7], b22 = (float)p.B[8];
+    const unsigned plane = (unsigned)p.oy * (unsigned)p.ox;
+    const int nx = p.mov.nx, ny = p.mov.ny, nz = p.mov.nz;
+    const uint32_t bar = smem_u32(&s_bar);
+    if (threadIdx.x == 0) {
+        mbar_init(bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    unsigned phase = 0;
+    const f32x2 magic2 = pk(kMagic, kMagic);
+
+    for (unsigned t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const int tz = (int)(t / (unsigned)(ntx * nty)), r2 = (int)(t % (unsigned)(ntx * nty));
+        const int i = (r2 % ntx) * 32 + lane, j = (r2 / ntx) * 8 + warp, k0 = tz * kTZ;
+        const bool row_ok = (i < p.ox) & (j < p.oy);
+        const int kcnt = row_ok ? min(kTZ, p.oz - k0) : 0;
+        // rigid part in float64 once per thread, split into integer base + float32 fraction (as make_row_ctx)
+        const double cx = ((A[3] + (double)k0 * A[2]) + (double)j * A[1]) + (double)i * A[0];
+        const double cy = ((A[7] + (double)k0 * A[6]) + (double)j * A[5]) + (double)i * A[4];
+        const double cz = ((A[11] + (double)k0 * A[10]) + (double)j * A[9]) + (double)i * A[8];
+        const RowCtx r = make_point_ctx(cx, cy, cz, nx, ny, nz);
+        const size_t v = ((size_t)k0 * p.oy + j) * p.ox + i;
+        // local coordinates of the 8 voxels (relative to the thread base r.b*), inside flags, clamped like BORDER tiles
+        float lx[kTZ], ly[kTZ], lz[kTZ];
+        unsigned inbits = 0u;
+        const float hix = CLOSED ? r.hix : prev_float(r.hix), hiy = CLOSED ? r.hiy : prev_float(r.hiy), hiz = CLOSED ? r.hiz : prev_float(r.hiz);
+        const float clox = -(float)r.bx, cloy = -(float)r.by, cloz = -(float)r.bz;
+        const float chix = (float)(nx - 1) - (float)r.bx, chiy = (float)(ny - 1) - (float)r.by, chiz = (float)(nz - 1) - (float)r.bz;
+        // Fast path (ncu: the first cut spent 80 lane-instructions per voxel in this phase, half of the kernel, on
+        // per-voxel inside tests, clamps and FRND / F2I for the bounding box): form the coordinates, take the thread's
+        // float min / max, and if all 8 voxels are strictly interior (no clamp, no test needed) floor only those six
+        // numbers.  Border columns, partial z tiles and fields that leave the volume take the per-voxel path.
+        float fmnx = INFINITY, fmny = INFINITY, fmnz = INFINITY, fmxx = -INFINITY, fmxy = -INFINITY, fmxz = -INFINITY;
+        {
+            const float *q = p.dvf + 3 * v;
+            float d[kTZ][3];
+#pragma unroll
+            for (int kz = 0; kz < kTZ; ++kz) {            // all field loads in flight first
+                const bool live = kz < kcnt;
+                d[kz][0] = live ? __ldg(q) : 0.0f;
+                d[kz][1] = live ? __ldg(q + 1) : 0.0f;
+                d[kz][2] = live ? __ldg(q + 2) : 0.0f;
+                q += 3 * (size_t)plane;
+            }
+#pragma unroll
+            for (int kz = 0; kz < kTZ; ++kz) {
+                lx[kz] = fmaf((float)kz, a2x, r.fx) + fmaf(b02, d[kz][2], fmaf(b01, d[kz][1], b00 * d[kz][0]));
+                ly[kz] = fmaf((float)kz, a2y, r.fy) + fmaf(b12, d[kz][2], fmaf(b11, d[kz][1], b10 * d[kz][0]));
+                lz[kz] = fmaf((float)kz, a2z, r.fz) + fmaf(b22, d[kz][2], fmaf(b21, d[kz][1], b20 * d[kz][0]));
+                fmnx = fminf(fmnx, lx[kz]); fmxx = fmaxf(fmxx, lx[kz]);
+                fmny = fminf(fmny, ly[kz]); fmxy = fmaxf(fmxy, ly[kz]);
+                fmnz = fminf(fmnz, lz[kz]); fmxz = fmaxf(fmxz, lz[kz]);
+            }
+        }
+        // NaN coordinates fail the comparisons below and take the per-voxel path, where they are outside
+        const bool interior = (kcnt == kTZ) & (fmnx >= clox) & (fmxx <= chix) & (fmny >= cloy) & (fmxy <= chiy) &
+                              (fmnz >= cloz) & (fmxz <= chiz);
+        if (interior) {
+            inbits = 0xffu;
+        } else {
+            fmnx = fmny = fmnz = INFINITY;
+            fmxx = fmxy = fmxz = -INFINITY;
+#pragma unroll
+            for (int kz = 0; kz < kTZ; ++kz) {
+                float x = lx[kz], y = ly[kz], z = lz[kz];
+                const bool in = (kz < kcnt) & (x >= r.lox) & (x <= hix) & (y >= r.loy) & (y <= hiy) & (z >= r.loz) & (z <= hiz);
+                x = fminf(fmaxf(x, clox), chix); y = fminf(fmaxf(y, cloy), chiy); z = fminf(fmaxf(z, cloz), chiz);
+                lx[kz] = x; ly[kz] = y; lz[kz] = z;
+                if (in) {
+                    inbits |= 1u << kz;
+                    fmnx = fminf(fmnx, x); fmxx = fmaxf(fmxx, x);
+                    fmny = fminf(fmny, y); fmxy = fmaxf(fmxy, y);
+                    fmnz = fminf(fmnz, z); fmxz = fmaxf(fmxz, z);
+                }
+            }
+        }
+        const int mnx = (int)floorf(fmnx), mxx = (int)floorf(fmxx), mny = (int)floorf(fmny), mxy = (int)floorf(fmxy),
+                  mnz = (int)floorf(fmnz), mxz = (int)floorf(fmxz);           // garbage when inbits == 0: not used then
+        // bounding box of the taps in moving index space: thread -> warp (REDUX) -> CTA
+        const bool any = inbits != 0u;
+        const int big = 0x7fffffff;
+        const int wmnx = __reduce_min_sync(0xffffffffu, any ? r.bx + mnx : big), wmxx = __reduce_max_sync(0xffffffffu, any ? r.bx + mxx : -big);
+        const int wmny = __reduce_min_sync(0xffffffffu, any ? r.by + mny : big), wmxy = __reduce_max_sync(0xffffffffu, any ? r.by + mxy : -big);
+        const int wmnz = __reduce_min_sync(0xffffffffu, any ? r.bz + mnz : big), wmxz = __reduce_max_sync(0xffffffffu, any ? r.bz + mxz : -big);
+        if (lane == 0) {
+            s_box[warp][0] = wmnx; s_box[warp][1] = wmxx; s_box[warp][2] = wmny;
+            s_box[warp][3] = wmxy; s_box[warp][4] = wmnz; s_box[warp][5] = wmxz;
+        }
+        __syncthreads();
+        int bx0 = big, bx1 = -big, by0 = big, by1 = -big, bz0 = big, bz1 = -big;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) {
+            bx0 = min(bx0, s_box[w][0]); bx1 = max(bx1, s_box[w][1]);
+            by0 = min(by0, s_box[w][2]); by1 = max(by1, s_box[w][3]);
+            bz0 = min(bz0, s_box[w][4]); bz1 = max(bz1, s_box[w][5]);
+        }
+        const bool none = bx0 == big;                          // CTA-uniform from here on
+        bx0 &= ~(xalign - 1);                                   // TMA: inner coordinate * element size = 0 mod 16 bytes
+        const bool fits = !none && (bx1 + 2 - bx0 <= BOX::kX) && (by1 + 2 - by0 <= BOX::kY) && (bz1 + 2 - bz0 <= BOX::kZ);
+        TO *o = out + v;
+        if (none) {
+#pragma unroll
+            for (int kz = 0; kz < kTZ; ++kz)
+                if (kz < kcnt) st_out(o + (size_t)kz * plane, bg);
+        } else if (!fits) {
+            // a tear in the field: per-voxel gather (coordinates were clamped above; weights beyond the edge are 0)
+#pragma unroll
+            for (int kz = 0; kz < kTZ; ++kz) {
+                if (kz < kcnt) {
+                    float val = 0.0f;
+                    const bool in = (inbits >> kz) & 1u;
+                    if (in) sample_local<TM, true>(mov, nx, ny, nz, r, lx[kz], ly[kz], lz[kz], val);
+                    st_out(o + (size_t)kz * plane, in ? tile_to_out<TO, CLOSED>(val) : bg);
+                }
+            }
+        } else {
+            if (threadIdx.x == 0) {
+                mbar_arrive_expect_tx(bar, kBoxBytes);
+                tma_load_3d(smem_u32(dsm), &tmap, bar, bx0, by0, bz0);
+            }
+            const int tbx = r.bx - bx0, tby = r.by - by0, tbz = r.bz - bz0;
+            const uint32_t ubase = smem_u32(dsm) + (uint32_t)((tbz * BOX::kY + tby) * BOX::kX + tbx) * ES + p.magic_fold;
+            // a voxel that is outside contributed nothing to the box, so it must not address beyond it either: its
+            // (unused) taps are taken at box element (0, 0, 0)
+            const float sx = (float)(-tbx), sy = (float)(-tby), sz = (float)(-tbz);
+            mbar_wait<64>(bar, phase);
+            phase ^= 1u;
+#pragma unroll
+            for (int kp = 0; kp < kTZ; kp += 2) {
+                const bool i0 = (inbits >> kp) & 1u, i1 = (inbits >> (kp + 1)) & 1u;
+                const f32x2 lx2 = pk(i0 ? lx[kp] : sx, i1 ? lx[kp + 1] : sx), ly2 = pk(i0 ? ly[kp] : sy, i1 ? ly[kp + 1] : sy),
+                            lz2 = pk(i0 ? lz[kp] : sz, i1 ? lz[kp + 1] : sz);
+                const f32x2 tx2 = add2_rm(lx2, magic2), ty2 = add2_rm(ly2, magic2), tz2 = add2_rm(lz2, magic2);
+                const f32x2 wx2 = sub2(lx2, sub2(tx2, magic2)), wy2 = sub2(ly2, sub2(ty2, magic2)), wz2 = sub2(lz2, sub2(tz2, magic2));
+                const uint32_t a0 = mad_u32(mad_u32(mad_u32((uint32_t)tz2, BOX::kY, (uint32_t)ty2), BOX::kX, (uint32_t)tx2), ES, ubase);
+                const uint32_t a1 = mad_u32(mad_u32(mad_u32((uint32_t)(tz2 >> 32), BOX::kY, (uint32_t)(ty2 >> 32)), BOX::kX, (uint32_t)(tx2 >> 32)), ES, ubase);
+                const f32x2 v000 = pk(Tap<TM, 0>::ld(a0), Tap<TM, 0>::ld(a1));
+                const f32x2 v100 = pk(Tap<TM, ES>::ld(a0), Tap<TM, ES>::ld(a1));
+                const f32x2 v010 = pk(Tap<TM, PY>::ld(a0), Tap<TM, PY>::ld(a1));
+                const f32x2 v110 = pk(Tap<TM, PY + ES>::ld(a0), Tap<TM, PY + ES>::ld(a1));
+                const f32x2 v001 = pk(Tap<TM, PZ>::ld(a0), Tap<TM, PZ>::ld(a1));
+                const f32x2 v101 = pk(Tap<TM, PZ + ES>::ld(a0), Tap<TM, PZ + ES>::ld(a1));
+                const f32x2 v011 = pk(Tap<TM, PZ + PY>::ld(a0), Tap<TM, PZ + PY>::ld(a1));
+                const f32x2 v111 = pk(Tap<TM, PZ + PY + ES>::ld(a0), Tap<TM, PZ + PY + ES>::ld(a1));
+                const f32x2 vx00 = lerp2(wx2, v000, v100), vx10 = lerp2(wx2, v010, v110);
+                const f32x2 vx01 = lerp2(wx2, v001, v101), vx11 = lerp2(wx2, v011, v111);
+                const f32x2 vxx0 = lerp2(wy2, vx00, vx10), vxx1 = lerp2(wy2, vx01, vx11);
+                float val0, val1;
+                upk(lerp2(wz2, vxx0, vxx1), val0, val1);
+                const TO o0 = tile_to_out<TO, CLOSED>(val0), o1 = tile_to_out<TO, CLOSED>(val1);
+                if (kp < kcnt) st_out(o, ((inbits >> kp) & 1u) ? o0 : bg);
+                o += plane;
+                if (kp + 1 < kcnt) st_out(o, ((inbits >> (kp + 1)) & 1u) ? o1 : bg);
+                o += plane;
+            }
+        }
+        __syncthreads();          // the box and s_box are free again
     }
 }
 

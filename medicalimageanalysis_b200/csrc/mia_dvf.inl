@@ -9,6 +9,34 @@ void launch_warp_dvf(const mia::DvfParams &p, int mode, unsigned grid, cudaStrea
     else mia::warp_dvf_kernel<TM, TO, false><<<grid, mia::kDvfThreads, 0, s>>>(p);
 }
 
+// Box-staged kernel (mia_dvf.cuh::warp_dvf_tile_kernel): needs a TMA descriptor of the image, like the rigid tile path.
+using DvfBoxI16 = mia::Box<96, 15, 14>;       // 40 KB: bank-friendly 96-short pitch (see TileCfg), 3 CTAs per SM
+using DvfBoxF32 = mia::Box<64, 14, 13>;       // 46.6 KB
+
+bool dvf_staged_disabled()
+{
+    static const bool off = [] { const char *e = getenv("MIA_DVF_DIRECT"); return e && *e && *e != '0'; }();
+    return off;
+}
+
+template <typename TM, class BOX>
+bool try_warp_dvf_staged(mia::DvfParams p, const void *d_mov, const int mdims[3], int mode, cudaStream_t s)
+{
+    if (dvf_staged_disabled() || tile_path_disabled()) return false;
+    alignas(64) CUtensorMap map;
+    if (!make_tensor_map<TM, BOX>(&map, d_mov, mdims)) return false;
+    const long long ntiles = (long long)((p.ox + 31) / 32) * ((p.oy + 7) / 8) * ((p.oz + mia::kTZ - 1) / mia::kTZ);
+    if (ntiles > 0x7fffffffLL || (long long)p.ox * p.oy * mia::kTZ >= 0x7fffffffLL) return false;
+    p.magic_fold = 0u - mia::kMagicBits * (unsigned)((BOX::kY + 1) * BOX::kX + 1) * (unsigned)sizeof(TM);
+    constexpr size_t smem = (size_t)BOX::kX * BOX::kY * BOX::kZ * sizeof(TM);
+    long long gx = (long long)sm_count() * MIA_DVF_STAGED_MINB;
+    if (gx > ntiles) gx = ntiles;
+    if (mode == MIA_MODE_VTK) mia::warp_dvf_tile_kernel<TM, TM, true, BOX><<<(unsigned)gx, mia::kDvfThreads, smem, s>>>(map, p);
+    else mia::warp_dvf_tile_kernel<TM, TM, false, BOX><<<(unsigned)gx, mia::kDvfThreads, smem, s>>>(map, p);
+    g_last_path = 3;
+    return true;
+}
+
 }  // namespace
 
 extern "C" {
@@ -40,6 +68,13 @@ int mia_warp_dvf(const void *d_mov, int mov_dtype, const int mdims[3], const flo
     long long gx = (long long)sm_count() * 8;
     if (gx > nwork) gx = nwork;
     cudaStream_t s = (cudaStream_t)stream;
+    g_last_path = 0;
+    const bool staged = mov_dtype == MIA_I16 ? try_warp_dvf_staged<int16_t, DvfBoxI16>(p, d_mov, mdims, mode, s)
+                                             : try_warp_dvf_staged<float, DvfBoxF32>(p, d_mov, mdims, mode, s);
+    if (staged) {
+        CUDA_TRY(cudaGetLastError());
+        return MIA_OK;
+    }
     if (mov_dtype == MIA_I16) launch_warp_dvf<int16_t, int16_t>(p, mode, (unsigned)gx, s);
     else launch_warp_dvf<float, float>(p, mode, (unsigned)gx, s);
     CUDA_TRY(cudaGetLastError());

@@ -110,3 +110,53 @@ def test_deformable_operators_follow_the_reference_recipe(cuda_device):
                                                   [vox[:, 2], vox[:, 1], vox[:, 0]], order=1, mode="nearest")
     assert np.allclose(moved, want_pts, rtol=0, atol=1e-11)
     Data.clear()
+
+
+@pytest.mark.parametrize("dtype", [np.int16, np.float32])
+@pytest.mark.parametrize("mode", ["itk", "vtk"])
+@pytest.mark.parametrize("kind", ["smooth", "tear", "far"])
+def test_box_staged_warp_matches_oracle(cuda_device, dtype, mode, kind):
+    """Row pitches the TMA unit accepts take the box-staged kernel (path 3): smooth fields stay inside the box, a field
+    with a tear sends the affected tiles to the per-voxel gather, a field that points out of the volume gives
+    background -- all against the oracle, and equal to the direct kernel up to float32 coordinate rounding."""
+    from medicalimageanalysis_b200 import _lib
+    shape, sp = (40, 56, 96), (1.0, 1.1, 2.0)
+    g, A, B = _case(shape, sp, 0)
+    img = make_phantom(shape, "CT", seed=14, spacing=sp).astype(dtype)
+    field = _smooth_field(shape, 4.0, 15)
+    if kind == "tear":
+        field[:, :, 40:, 0] += 37.0                                  # a jump of 37 mm across one voxel column
+        field[20:, 28:, :, 2] -= 24.0
+    if kind == "far":
+        field[:6] += 400.0                                           # the first planes leave the volume altogether
+        field[:, :5, :, 1] -= 2.0 * sp[1]                            # and a strip straddles the lower y border
+    t, f = torch.from_numpy(img).to(cuda_device), torch.from_numpy(field).to(cuda_device)
+    got = kernels.warp_dvf(t, f, A, B, background=-3001.0, mode=mode).cpu().numpy()
+    assert _lib.load().mia_debug_last_path() == 3
+    want = D.oracle_warp_dvf(img, field, A, B, background=-3001.0, mode=mode)
+    edge = (got == -3001) != (want == -3001)
+    assert edge.mean() < 1e-4
+    if kind == "far":
+        assert (want == -3001).mean() > 0.1
+    if dtype == np.int16:
+        d = np.abs(got.astype(np.int32) - want.astype(np.int32))
+        assert d[~edge].max() <= 1 and (d[~edge] > 0).mean() < 2e-3
+    else:
+        assert np.allclose(got[~edge], want[~edge], rtol=1e-4, atol=1e-2)
+
+
+def test_box_staged_warp_identity_translation_and_partial_tiles(cuda_device):
+    from medicalimageanalysis_b200 import _lib
+    shape, sp = (21, 45, 72), (1.0, 1.0, 2.5)                         # partial tiles in y and z, full rows of 72
+    g, A, B = _case(shape, sp, 0)
+    img = make_phantom(shape, "CT", seed=16, spacing=sp)
+    t = torch.from_numpy(img).to(cuda_device)
+    zero = torch.zeros(shape + (3,), dtype=torch.float32, device=cuda_device)
+    assert torch.equal(kernels.warp_dvf(t, zero, A, B, mode="itk"), t)
+    assert _lib.load().mia_debug_last_path() == 3
+    shift = np.array([2.0, -3.0, 5.0], dtype=np.float32)
+    const = torch.from_numpy(np.broadcast_to(shift, shape + (3,)).copy()).to(cuda_device)
+    As = A.copy()
+    As[:, 3] += B @ shift.astype(np.float64)
+    assert torch.equal(kernels.warp_dvf(t, const, A, B, background=-3001.0, mode="itk"),
+                       kernels.resample(t, As, shape, background=-3001.0, mode="itk"))
