@@ -123,7 +123,8 @@ __global__ void __launch_bounds__(kDvfThreads, MIA_DVF_MINB) warp_dvf_kernel(con
 #ifndef MIA_DVF_STAGED_MINB
 #define MIA_DVF_STAGED_MINB 3
 #endif
-template <typename TM, typename TO, bool CLOSED, class BOX>
+// DIAG: B is diagonal (image axes along the physical axes, the usual case): one FFMA per axis instead of three.
+template <typename TM, typename TO, bool CLOSED, class BOX, bool DIAG>
 __global__ void __launch_bounds__(kDvfThreads, MIA_DVF_STAGED_MINB)
 warp_dvf_tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ DvfParams p)
 {
@@ -182,19 +183,37 @@ warp_dvf_tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
         {
             const float *q = p.dvf + 3 * v;
             float d[kTZ][3];
+            if (kcnt == kTZ) {                            // full column: no predicates, one stepped 64-bit pointer
 #pragma unroll
-            for (int kz = 0; kz < kTZ; ++kz) {            // all field loads in flight first
-                const bool live = kz < kcnt;
-                d[kz][0] = live ? __ldg(q) : 0.0f;
-                d[kz][1] = live ? __ldg(q + 1) : 0.0f;
-                d[kz][2] = live ? __ldg(q + 2) : 0.0f;
-                q += 3 * (size_t)plane;
+                for (int kz = 0; kz < kTZ; ++kz) {        // all field loads in flight first
+                    asm("" : "+l"(q));
+                    d[kz][0] = __ldg(q);
+                    d[kz][1] = __ldg(q + 1);
+                    d[kz][2] = __ldg(q + 2);
+                    q += 3u * plane;
+                }
+            } else {
+#pragma unroll
+                for (int kz = 0; kz < kTZ; ++kz) {
+                    const bool live = kz < kcnt;
+                    d[kz][0] = live ? __ldg(q) : 0.0f;
+                    d[kz][1] = live ? __ldg(q + 1) : 0.0f;
+                    d[kz][2] = live ? __ldg(q + 2) : 0.0f;
+                    q += 3u * plane;
+                }
             }
 #pragma unroll
             for (int kz = 0; kz < kTZ; ++kz) {
-                lx[kz] = fmaf((float)kz, a2x, r.fx) + fmaf(b02, d[kz][2], fmaf(b01, d[kz][1], b00 * d[kz][0]));
-                ly[kz] = fmaf((float)kz, a2y, r.fy) + fmaf(b12, d[kz][2], fmaf(b11, d[kz][1], b10 * d[kz][0]));
-                lz[kz] = fmaf((float)kz, a2z, r.fz) + fmaf(b22, d[kz][2], fmaf(b21, d[kz][1], b20 * d[kz][0]));
+                const float rx = fmaf((float)kz, a2x, r.fx), ry = fmaf((float)kz, a2y, r.fy), rz = fmaf((float)kz, a2z, r.fz);
+                if (DIAG) {
+                    lx[kz] = fmaf(b00, d[kz][0], rx);
+                    ly[kz] = fmaf(b11, d[kz][1], ry);
+                    lz[kz] = fmaf(b22, d[kz][2], rz);
+                } else {
+                    lx[kz] = rx + fmaf(b02, d[kz][2], fmaf(b01, d[kz][1], b00 * d[kz][0]));
+                    ly[kz] = ry + fmaf(b12, d[kz][2], fmaf(b11, d[kz][1], b10 * d[kz][0]));
+                    lz[kz] = rz + fmaf(b22, d[kz][2], fmaf(b21, d[kz][1], b20 * d[kz][0]));
+                }
                 fmnx = fminf(fmnx, lx[kz]); fmxx = fmaxf(fmxx, lx[kz]);
                 fmny = fminf(fmny, ly[kz]); fmxy = fmaxf(fmxy, ly[kz]);
                 fmnz = fminf(fmnz, lz[kz]); fmxz = fmaxf(fmxz, lz[kz]);

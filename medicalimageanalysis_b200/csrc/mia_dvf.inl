@@ -31,8 +31,18 @@ bool try_warp_dvf_staged(mia::DvfParams p, const void *d_mov, const int mdims[3]
     constexpr size_t smem = (size_t)BOX::kX * BOX::kY * BOX::kZ * sizeof(TM);
     long long gx = (long long)sm_count() * MIA_DVF_STAGED_MINB;
     if (gx > ntiles) gx = ntiles;
-    if (mode == MIA_MODE_VTK) mia::warp_dvf_tile_kernel<TM, TM, true, BOX><<<(unsigned)gx, mia::kDvfThreads, smem, s>>>(map, p);
-    else mia::warp_dvf_tile_kernel<TM, TM, false, BOX><<<(unsigned)gx, mia::kDvfThreads, smem, s>>>(map, p);
+    // the float32 image of B decides; the diagonal kernel differs from the general one by one float32 rounding of a
+    // local coordinate (~1e-7 voxel)
+    const bool diag = (float)p.B[1] == 0.0f && (float)p.B[2] == 0.0f && (float)p.B[3] == 0.0f && (float)p.B[5] == 0.0f &&
+                      (float)p.B[6] == 0.0f && (float)p.B[7] == 0.0f;
+    const unsigned g = (unsigned)gx;
+    if (mode == MIA_MODE_VTK) {
+        if (diag) mia::warp_dvf_tile_kernel<TM, TM, true, BOX, true><<<g, mia::kDvfThreads, smem, s>>>(map, p);
+        else mia::warp_dvf_tile_kernel<TM, TM, true, BOX, false><<<g, mia::kDvfThreads, smem, s>>>(map, p);
+    } else {
+        if (diag) mia::warp_dvf_tile_kernel<TM, TM, false, BOX, true><<<g, mia::kDvfThreads, smem, s>>>(map, p);
+        else mia::warp_dvf_tile_kernel<TM, TM, false, BOX, false><<<g, mia::kDvfThreads, smem, s>>>(map, p);
+    }
     g_last_path = 3;
     return true;
 }
