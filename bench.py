@@ -322,7 +322,32 @@ def extras(dev, torch, kernels, peak):
             "hbm_frac_per_eval": 8.0 * nv * res.evaluations / dt / 1e9 / peak,
             "final_params": [round(float(x), 3) for x in res.params], "gt_params": list(gt3),
             "cost_first": float(res.cost_history[0]), "cost_last": float(res.cost_history[-1])}
+    # config 3 with the Mattes (Parzen-window) metric, coarse-to-fine over a 2-level pyramid
+    cfgm = RegistrationConfig(metric="mattes", iterations=100, bins=50, graph_iters=10)
+    R.register_rigid_multires(f3, m3, cfg=RegistrationConfig(metric="mattes", iterations=20, bins=50), shrink_factors=(2, 1))
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    res = R.register_rigid_multires(f3, m3, cfg=cfgm, shrink_factors=(2, 1))
+    torch.cuda.synchronize(dev)
+    dt = time.perf_counter() - t0
+    out["c3_register_mattes_multires"] = {
+        "iters_per_s": 200 / dt, "evals_per_s": res.evaluations / dt, "levels": "(2,2,2) x 100 + (1,1,1) x 100 iterations",
+        "final_params": [round(float(x), 3) for x in res.params], "gt_params": list(gt3)}
     Data.clear()
+    del f3, m3
+
+    # the C2 volume through a smooth displacement field (12 + 2 + 2 algorithmic bytes per voxel)
+    z, y, x = (torch.arange(n, device=dev, dtype=torch.float32) for n in SHAPE)
+    img = (600 * torch.sin(x[None, None, :] / 17) * torch.cos(y[None, :, None] / 23) * torch.sin(z[:, None, None] / 19)).to(torch.int16)
+    field = torch.stack([4 * torch.sin(x[None, None, :] / 40 + c) * torch.cos(y[None, :, None] / 50) * torch.sin(z[:, None, None] / 30 + c)
+                         for c in range(3)], dim=-1).contiguous()
+    gd = G.Grid((SHAPE[2], SHAPE[1], SHAPE[0]), SPACING, (0.0, 0.0, 0.0))
+    w2p = G.physical_to_index(gd, "itk")
+    Ad, Bd = (w2p @ G.index_to_physical(gd, "itk"))[:3], w2p[:3, :3]
+    od = torch.empty_like(img)
+    t = time_launches(lambda: kernels.warp_dvf(img, field, Ad, Bd, out=od))
+    out["n1_warp_dvf_i16"] = {"gvoxel_s": img.numel() / t / 1e9, "hbm_frac": 16.0 * img.numel() / t / 1e9 / peak, "us": t * 1e6}
+    del img, field, od
     return out
 
 
