@@ -219,17 +219,20 @@ int mia_shrink_mean(const void *d_in, int dtype, const int idims[3], void *d_out
  * SURVEY N5 -- fixed-image masks for the fused metrics (SetMetricFixedMask / elastix SetFixedMask,
  * utils/deformable/simpleitk.py:116-117, 146-147).  Same arguments as mia_resample_ssd / mia_resample_jointhist
  * plus d_fixed_mask: uint8 [z][y][x] on the fixed lattice, 0 = the voxel takes no part in the metric (NULL = no
- * mask).  A masked SSD does not store the resampled volume (d_out must be NULL).
+ * mask), and d_moving_mask (SetMetricMovingMask, :118-119, 148-149): uint8 on the MOVING lattice, looked up at the
+ * voxel nearest to the mapped point (floor(c + 0.5)); a launch with a moving mask runs on the per-voxel kernel.
+ * A masked SSD does not store the resampled volume (d_out must be NULL).
  */
 int mia_resample_ssd_masked(const void *d_mov, int mov_dtype, const int mdims[3], const void *d_fixed,
-                            int fixed_dtype, const unsigned char *d_fixed_mask, const int odims[3], void *d_out,
-                            int out_dtype, int n_mats, const double *A, const double *d_A, double background, int mode,
-                            double *d_ssd, unsigned long long *d_count, void *d_ws, size_t ws_bytes, void *stream);
+                            int fixed_dtype, const unsigned char *d_fixed_mask, const unsigned char *d_moving_mask,
+                            const int odims[3], void *d_out, int out_dtype, int n_mats, const double *A, const double *d_A,
+                            double background, int mode, double *d_ssd, unsigned long long *d_count, void *d_ws,
+                            size_t ws_bytes, void *stream);
 int mia_resample_jointhist_masked(const void *d_mov, int mov_dtype, const int mdims[3], const void *d_fixed,
-                                  int fixed_dtype, const unsigned char *d_fixed_mask, const int odims[3], int n_mats,
-                                  const double *A, const double *d_A, int mode, float fmin, float fmax, float mmin,
-                                  float mmax, int bins, unsigned int *d_hist, unsigned long long *d_count, void *d_ws,
-                                  size_t ws_bytes, void *stream);
+                                  int fixed_dtype, const unsigned char *d_fixed_mask, const unsigned char *d_moving_mask,
+                                  const int odims[3], int n_mats, const double *A, const double *d_A, int mode, float fmin,
+                                  float fmax, float mmin, float mmax, int bins, unsigned int *d_hist,
+                                  unsigned long long *d_count, void *d_ws, size_t ws_bytes, void *stream);
 
 /*
  * SURVEY N5 -- Mattes mutual information ("AdvancedMattesMutualInformation" + NumberOfHistogramBins,
@@ -238,12 +241,13 @@ int mia_resample_jointhist_masked(const void *d_mov, int mov_dtype, const int md
  * the moving image.  The B-spline is evaluated on a 1/256 sub-bin lattice with integer weights that sum to 1024 per
  * sample, so d_hist ([n][bins][bins] uint64, units of 1/1024 sample) is an INTEGER histogram: bit-identical for
  * every grid, sharding and GPU count; d_count[n] = samples.  mia_mi_from_hist64 turns it into MI (nats).
- * d_fixed_mask may be NULL.
+ * d_fixed_mask and d_moving_mask may be NULL (semantics as in mia_resample_ssd_masked).
  */
 int mia_resample_mattes(const void *d_mov, int mov_dtype, const int mdims[3], const void *d_fixed, int fixed_dtype,
-                        const unsigned char *d_fixed_mask, const int odims[3], int n_mats, const double *A,
-                        const double *d_A, int mode, float fmin, float fmax, float mmin, float mmax, int bins,
-                        unsigned long long *d_hist, unsigned long long *d_count, void *d_ws, size_t ws_bytes, void *stream);
+                        const unsigned char *d_fixed_mask, const unsigned char *d_moving_mask, const int odims[3],
+                        int n_mats, const double *A, const double *d_A, int mode, float fmin, float fmax, float mmin,
+                        float mmax, int bins, unsigned long long *d_hist, unsigned long long *d_count, void *d_ws,
+                        size_t ws_bytes, void *stream);
 int mia_mi_from_hist64(const unsigned long long *d_hist, int bins, int n_mats, double *d_mi, void *stream);
 
 /* Page-locked host buffers for the *_host entry point (a NumPy array can wrap them). */

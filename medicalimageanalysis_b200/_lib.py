@@ -33,12 +33,12 @@ SIGNATURES = {
     "mia_resample_ssd": (_i, [_vp, _i, _ip, _vp, _i, _ip, _vp, _i, _i, _dp, _vp, _d, _i, _vp, _vp, _vp, _sz, _vp]),
     "mia_resample_jointhist": (_i, [_vp, _i, _ip, _vp, _i, _ip, _i, _dp, _vp, _i, _f, _f, _f, _f, _i, _vp, _vp,
                                     _vp, _sz, _vp]),
-    "mia_resample_ssd_masked": (_i, [_vp, _i, _ip, _vp, _i, _vp, _ip, _vp, _i, _i, _dp, _vp, _d, _i, _vp, _vp, _vp, _sz,
-                                     _vp]),
-    "mia_resample_jointhist_masked": (_i, [_vp, _i, _ip, _vp, _i, _vp, _ip, _i, _dp, _vp, _i, _f, _f, _f, _f, _i, _vp,
-                                           _vp, _vp, _sz, _vp]),
-    "mia_resample_mattes": (_i, [_vp, _i, _ip, _vp, _i, _vp, _ip, _i, _dp, _vp, _i, _f, _f, _f, _f, _i, _vp, _vp, _vp, _sz,
-                                 _vp]),
+    "mia_resample_ssd_masked": (_i, [_vp, _i, _ip, _vp, _i, _vp, _vp, _ip, _vp, _i, _i, _dp, _vp, _d, _i, _vp, _vp, _vp,
+                                     _sz, _vp]),
+    "mia_resample_jointhist_masked": (_i, [_vp, _i, _ip, _vp, _i, _vp, _vp, _ip, _i, _dp, _vp, _i, _f, _f, _f, _f, _i,
+                                           _vp, _vp, _vp, _sz, _vp]),
+    "mia_resample_mattes": (_i, [_vp, _i, _ip, _vp, _i, _vp, _vp, _ip, _i, _dp, _vp, _i, _f, _f, _f, _f, _i, _vp, _vp, _vp,
+                                 _sz, _vp]),
     "mia_mi_from_hist64": (_i, [_vp, _i, _i, _vp, _vp]),
     "mia_mi_from_hist": (_i, [_vp, _i, _i, _vp, _vp]),
     "mia_optimizer_state_bytes": (_sz, []),

@@ -337,6 +337,20 @@ int try_tile_box(int mode, const void *d_mov, const int mdims[3], const double *
 #ifndef MIA_MULTI_F32
 #define MIA_MULTI_F32 2, 2
 #endif
+// The multi-matrix kernel has its own int16 box, two planes deeper than the one-matrix SSD box: it has the shared memory
+// of a whole SM, and the z slack decides how many probes of a large isotropic lattice share a box (mia_tile_multi.cuh).
+#ifndef MIA_MULTI_BOX_I16_Z
+#define MIA_MULTI_BOX_I16_Z 14
+#endif
+#ifndef MIA_MULTI_BOX_I16
+#define MIA_MULTI_BOX_I16 96, 15, MIA_MULTI_BOX_I16_Z
+#endif
+#ifndef MIA_MULTI_BOX_F32
+#define MIA_MULTI_BOX_F32 64, 15, 14
+#endif
+template <typename TM> struct MultiBox;
+template <> struct MultiBox<int16_t> { using BOX = Box<MIA_MULTI_BOX_I16>; };
+template <> struct MultiBox<float> { using BOX = Box<MIA_MULTI_BOX_F32>; };
 template <int NST_, int G_> struct MultiCfgT { static constexpr int NST = NST_, G = G_; };
 template <typename TM> struct MultiCfg;
 template <> struct MultiCfg<int16_t> : MultiCfgT<MIA_MULTI_I16> {};
@@ -345,7 +359,7 @@ template <> struct MultiCfg<float> : MultiCfgT<MIA_MULTI_F32> {};
 template <typename TM, bool VTK, bool MASK = false>
 int launch_multi(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream_t s)
 {
-    using BOX = typename TileCfg<TM, kSsd>::BOX;
+    using BOX = typename MultiBox<TM>::BOX;
     constexpr int NST = MultiCfg<TM>::NST, G = MultiCfg<TM>::G;
     constexpr int threads = 32 * (kConsumerWarps * G + 1);
     auto k = tile_multi_kernel<TM, TM, VTK, BOX, NST, G, MASK>;
@@ -386,7 +400,7 @@ template <typename TM>
 int try_multi_t(int mode, const void *d_mov, const int mdims[3], const double *A_host, int n_mats, KParams p,
                 cudaStream_t s, bool &launched)
 {
-    using BOX = typename TileCfg<TM, kSsd>::BOX;
+    using BOX = typename MultiBox<TM>::BOX;
     launched = false;
     alignas(64) CUtensorMap map;
     for (int m = 0; A_host && m < n_mats; ++m)
@@ -518,17 +532,19 @@ int mia_resample_ssd(const void *d_mov, int mov_dtype, const int mdims[3], const
                      const double *A, const double *d_A, double background, int mode, double *d_ssd,
                      unsigned long long *d_count, void *d_ws, size_t ws_bytes, void *stream)
 {
-    return mia_resample_ssd_masked(d_mov, mov_dtype, mdims, d_fixed, fixed_dtype, nullptr, odims, d_out, out_dtype, n_mats, A,
+    return mia_resample_ssd_masked(d_mov, mov_dtype, mdims, d_fixed, fixed_dtype, nullptr, nullptr, odims, d_out, out_dtype, n_mats, A,
                                    d_A, background, mode, d_ssd, d_count, d_ws, ws_bytes, stream);
 }
 
 int mia_resample_ssd_masked(const void *d_mov, int mov_dtype, const int mdims[3], const void *d_fixed,
-                            int fixed_dtype, const unsigned char *d_fixed_mask, const int odims[3], void *d_out,
-                            int out_dtype, int n_mats, const double *A, const double *d_A, double background, int mode,
-                            double *d_ssd, unsigned long long *d_count, void *d_ws, size_t ws_bytes, void *stream)
+                            int fixed_dtype, const unsigned char *d_fixed_mask, const unsigned char *d_moving_mask,
+                            const int odims[3], void *d_out, int out_dtype, int n_mats, const double *A, const double *d_A,
+                            double background, int mode, double *d_ssd, unsigned long long *d_count, void *d_ws,
+                            size_t ws_bytes, void *stream)
 {
     cudaStream_t s = (cudaStream_t)stream;
-    if (d_out && d_fixed_mask) return fail(MIA_ERR_UNSUPPORTED, "mia_resample_ssd_masked: a masked metric does not store");
+    if (d_out && (d_fixed_mask || d_moving_mask))
+        return fail(MIA_ERR_UNSUPPORTED, "mia_resample_ssd_masked: a masked metric does not store");
     if (!d_ssd || !d_count) return fail(MIA_ERR_ARG, "mia_resample_ssd: null result pointer");
     if (d_out && n_mats != 1) return fail(MIA_ERR_ARG, "mia_resample_ssd: storing needs n_mats == 1");
     if (d_out && out_dtype != mov_dtype)
@@ -539,6 +555,7 @@ int mia_resample_ssd_masked(const void *d_mov, int mov_dtype, const int mdims[3]
                            A, d_A, mode, d_ws, ws_bytes, s, w);
     if (rc) return rc;
     p.fmask = d_fixed_mask;
+    p.mmask = d_moving_mask;
     p.out = d_out;
     p.background = (float)background;
     p.d_ssd = d_ssd;
@@ -548,7 +565,7 @@ int mia_resample_ssd_masked(const void *d_mov, int mov_dtype, const int mdims[3]
     if (gx > kMaxGridX) gx = kMaxGridX;
     dim3 grid((unsigned)gx, (unsigned)n_mats, 1);
     g_last_path = 0;
-    if (mov_dtype == fixed_dtype) {
+    if (mov_dtype == fixed_dtype && !p.mmask) {          // a moving mask runs on the per-voxel kernel
         bool launched = false;
         if (!d_out) {
             const int mrc = try_multi(mov_dtype, mode, d_mov, mdims, d_A ? nullptr : A, n_mats, p, s, launched);
@@ -570,15 +587,15 @@ int mia_resample_jointhist(const void *d_mov, int mov_dtype, const int mdims[3],
                            int bins, unsigned int *d_hist, unsigned long long *d_count, void *d_ws,
                            size_t ws_bytes, void *stream)
 {
-    return mia_resample_jointhist_masked(d_mov, mov_dtype, mdims, d_fixed, fixed_dtype, nullptr, odims, n_mats, A, d_A, mode,
+    return mia_resample_jointhist_masked(d_mov, mov_dtype, mdims, d_fixed, fixed_dtype, nullptr, nullptr, odims, n_mats, A, d_A, mode,
                                          fmin, fmax, mmin, mmax, bins, d_hist, d_count, d_ws, ws_bytes, stream);
 }
 
 int mia_resample_jointhist_masked(const void *d_mov, int mov_dtype, const int mdims[3], const void *d_fixed,
-                                  int fixed_dtype, const unsigned char *d_fixed_mask, const int odims[3], int n_mats,
-                                  const double *A, const double *d_A, int mode, float fmin, float fmax, float mmin,
-                                  float mmax, int bins, unsigned int *d_hist, unsigned long long *d_count, void *d_ws,
-                                  size_t ws_bytes, void *stream)
+                                  int fixed_dtype, const unsigned char *d_fixed_mask, const unsigned char *d_moving_mask,
+                                  const int odims[3], int n_mats, const double *A, const double *d_A, int mode, float fmin,
+                                  float fmax, float mmin, float mmax, int bins, unsigned int *d_hist,
+                                  unsigned long long *d_count, void *d_ws, size_t ws_bytes, void *stream)
 {
     cudaStream_t s = (cudaStream_t)stream;
     if (!d_hist || !d_count) return fail(MIA_ERR_ARG, "mia_resample_jointhist: null result pointer");
@@ -590,6 +607,7 @@ int mia_resample_jointhist_masked(const void *d_mov, int mov_dtype, const int md
                            n_mats, A, d_A, mode, d_ws, ws_bytes, s, w);
     if (rc) return rc;
     p.fmask = d_fixed_mask;
+    p.mmask = d_moving_mask;
     p.d_hist = d_hist;
     p.d_count = d_count;
     p.bins = bins;
@@ -602,7 +620,7 @@ int mia_resample_jointhist_masked(const void *d_mov, int mov_dtype, const int md
     if (gx > kMaxGridX) gx = kMaxGridX;
     dim3 grid((unsigned)gx, (unsigned)n_mats, 1);
     g_last_path = 0;
-    if (mov_dtype == fixed_dtype) {
+    if (mov_dtype == fixed_dtype && !p.mmask) {
         bool launched = false;
         const int trc = try_tile<kHist, false>(mov_dtype, mode, d_mov, mdims, d_A ? nullptr : A, n_mats, p, s, launched);
         if (launched) return trc;
@@ -633,9 +651,10 @@ int mia_mi_from_hist64(const unsigned long long *d_hist, int bins, int n_mats, d
 }
 
 int mia_resample_mattes(const void *d_mov, int mov_dtype, const int mdims[3], const void *d_fixed, int fixed_dtype,
-                        const unsigned char *d_fixed_mask, const int odims[3], int n_mats, const double *A,
-                        const double *d_A, int mode, float fmin, float fmax, float mmin, float mmax, int bins,
-                        unsigned long long *d_hist, unsigned long long *d_count, void *d_ws, size_t ws_bytes, void *stream)
+                        const unsigned char *d_fixed_mask, const unsigned char *d_moving_mask, const int odims[3],
+                        int n_mats, const double *A, const double *d_A, int mode, float fmin, float fmax, float mmin,
+                        float mmax, int bins, unsigned long long *d_hist, unsigned long long *d_count, void *d_ws,
+                        size_t ws_bytes, void *stream)
 {
     cudaStream_t s = (cudaStream_t)stream;
     if (!d_hist || !d_count) return fail(MIA_ERR_ARG, "mia_resample_mattes: null result pointer");
@@ -647,6 +666,7 @@ int mia_resample_mattes(const void *d_mov, int mov_dtype, const int mdims[3], co
                            mode, d_ws, ws_bytes, s, w);
     if (rc) return rc;
     p.fmask = d_fixed_mask;
+    p.mmask = d_moving_mask;
     p.d_hist64 = d_hist;
     p.d_count = d_count;
     p.bins = bins;
@@ -661,7 +681,7 @@ int mia_resample_mattes(const void *d_mov, int mov_dtype, const int mdims[3], co
     if (gx > kMaxGridX) gx = kMaxGridX;
     dim3 grid((unsigned)gx, (unsigned)n_mats, 1);
     g_last_path = 0;
-    if (mov_dtype == fixed_dtype) {
+    if (mov_dtype == fixed_dtype && !p.mmask) {
         bool launched = false;
         const int trc = try_tile<kMattes, false>(mov_dtype, mode, d_mov, mdims, d_A ? nullptr : A, n_mats, p, s, launched);
         if (launched) return trc;

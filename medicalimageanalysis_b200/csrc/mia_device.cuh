@@ -136,6 +136,17 @@ __device__ __forceinline__ bool sample_voxel(const TM *__restrict__ mov, int nx,
                                     fmaf((float)v, r.az, r.fz), val);
 }
 
+// Moving-image mask at the mapped point of voxel v: the mask voxel nearest to the continuous index (floor(c + 0.5),
+// ITK's RoundHalfIntegerUp), clamped to the volume like the taps.
+__device__ __forceinline__ bool nearest_mask_voxel(const unsigned char *__restrict__ mask, int nx, int ny, int nz,
+                                                   const RowCtx &r, int v)
+{
+    const int ix = clampi(r.bx + (int)floorf(fmaf((float)v, r.ax, r.fx) + 0.5f), 0, nx - 1);
+    const int iy = clampi(r.by + (int)floorf(fmaf((float)v, r.ay, r.fy) + 0.5f), 0, ny - 1);
+    const int iz = clampi(r.bz + (int)floorf(fmaf((float)v, r.az, r.fz) + 0.5f), 0, nz - 1);
+    return __ldg(mask + ((size_t)iz * ny + iy) * nx + ix) != 0;
+}
+
 // float -> output element.  ROUND: 0 = floor(v + 0.5) (VTK), 1 = trunc (ITK); clamp to the type range first.
 template <typename TO>
 __device__ __forceinline__ TO to_out(float v, int round_mode);

@@ -10,6 +10,8 @@ struct KParams {
     VolView mov;                 // moving volume
     const void *fixed;           // fixed volume on the output lattice (metrics) or nullptr
     const unsigned char *fmask;  // optional fixed-image mask on the output lattice (metrics): 0 = voxel ignored
+    const unsigned char *mmask;  // optional moving-image mask on the moving lattice, looked up at the nearest voxel of
+                                 // the mapped point (per-voxel kernel only)
     void *out;                   // resampled output or nullptr
     int ox, oy, oz;              // output lattice
     int ntx, nty;                // tiles along x / y
@@ -156,7 +158,8 @@ __global__ void __launch_bounds__(kThreads) resample_kernel(const KParams p)
             float val;
             bool live = full || (i0 + v >= 0 && i0 + v < p.ox);
             if (METRIC != kNone && p.fmask && live) live = __ldg(p.fmask + rowbase + i0 + v) != 0;
-            const bool in = live && sample_voxel<TM, CLOSED>(mov, nx, ny, nz, r, v, val);
+            bool in = live && sample_voxel<TM, CLOSED>(mov, nx, ny, nz, r, v, val);
+            if (METRIC != kNone && p.mmask && in) in = nearest_mask_voxel(p.mmask, nx, ny, nz, r, v);
             if (STORE) o.v[v] = in ? to_out<TO>(val, p.round_mode) : to_out<TO>(p.background, p.round_mode);
             if (METRIC == kSsd && in) {
                 const float d = fv[v] - val;

@@ -9,6 +9,14 @@
 // fixed-image values held in registers.  Matrices whose tile does not fit the shared box fall back to the
 // per-voxel gather for that tile, so unrelated matrices stay correct (just slow).
 //
+// Boxes per tile position.  The probes of one iteration drift apart with the distance from the rotation centre: on a
+// 1024 x 1024 x 1200 lattice of 0.5 mm voxels a +-0.5 degree probe moves the far tiles by +-4.5 voxels, and one box
+// with 2 voxels of slack in z then serves only 8.75 of the 13 matrices on average -- the other 4.25 took the per-voxel
+// gather at a third of the speed (measured: 283 Gvoxel/s on config 5 against 425 on config 1).  The producer
+// therefore partitions the matrices of a tile position into up to kMultiBoxes groups that each share a box, one ring
+// stage per group (a header word per stage tells the consumers whether the tile position is finished); with the
+// deeper int16 box (MultiBox) 0.2 matrices per tile are left for the gather on that lattice.
+//
 // Per-voxel arithmetic is tile_compute, unchanged: thread coordinates are taken relative to the box origin in
 // Q31.32 fixed point, and an integer change of that origin does not change any fraction, so every voxel value
 // is bit-identical to what tile_kernel computes for the same matrix.
@@ -18,6 +26,10 @@
 namespace mia {
 
 constexpr int kMaxMulti = 16;      // matrices per launch on this path (lane = matrix in the producer warp)
+#ifndef MIA_MULTI_BOXES
+#define MIA_MULTI_BOXES 3
+#endif
+constexpr int kMultiBoxes = MIA_MULTI_BOXES;     // boxes (ring stages) per tile position at most
 
 // One CTA per SM: G groups of 8 consumer warps share every staged box (group g takes matrices g, g+G, ...), one
 // producer warp feeds the ring.  More resident warps than two independent CTAs could hold (their rings would not
@@ -32,7 +44,8 @@ struct MultiSmem {
     static constexpr unsigned kBarOff = kStageBytes * NST;
     static constexpr unsigned kInfoOff = kBarOff + 16u * NST;                                  // TileInfo[NST][kMaxMulti]
     static constexpr unsigned kMatOff = kInfoOff + (unsigned)sizeof(TileInfo) * NST * kMaxMulti;   // double[kMaxMulti][12]
-    static constexpr unsigned kAccOff = kMatOff + 8u * 12u * kMaxMulti;                        // double[G][kMaxMulti][256]
+    static constexpr unsigned kHdrOff = kMatOff + 8u * 12u * kMaxMulti;                        // unsigned[NST]: 1 = last stage of its tile
+    static constexpr unsigned kAccOff = kHdrOff + 64u;                                         // double[G][kMaxMulti][256]
     static constexpr unsigned kCntOff = kAccOff + 8u * G * kMaxMulti * kMultiLanes;            // unsigned[G][kMaxMulti][256]
     static constexpr unsigned kBytes = kCntOff + 4u * G * kMaxMulti * kMultiLanes;
 };
@@ -50,6 +63,8 @@ tile_multi_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constan
     const int grp = wid / kConsumerWarps, warp = wid % kConsumerWarps;      // consumer group, y row inside the tile
     TileInfo *infos = reinterpret_cast<TileInfo *>(tsm + L::kInfoOff);
     double *s_A = reinterpret_cast<double *>(tsm + L::kMatOff);
+    volatile unsigned *s_hdr = reinterpret_cast<volatile unsigned *>(tsm + L::kHdrOff);
+    static_assert(NST <= 16, "header words");
     double *s_acc = reinterpret_cast<double *>(tsm + L::kAccOff);
     unsigned *s_cnt = reinterpret_cast<unsigned *>(tsm + L::kCntOff);
     const uint32_t bar0 = smem_u32(tsm + L::kBarOff);       // full[s] = bar0 + 8 s, empty[s] = bar0 + 8 (NST + s)
@@ -95,45 +110,55 @@ tile_multi_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constan
         for (int n = 0; n < ntile_mine; ++n) {
             const TileAabb bb = tile_aabb(A, reach, tix * kTX, tiy * kTY, tiz * kTZ, p.mov.nx, p.mov.ny, p.mov.nz);
             const bool active = have && !bb.outside;
-            const unsigned amask = __ballot_sync(0xffffffffu, active);
-            TileInfo mine;
-            mine.rx = mine.ry = mine.rz = 0;
-            mine.bx = mine.by = mine.bz = 0;
-            mine.cls = kOutside;
-            unsigned boxmask = 0;
-            int ox = 0, oy = 0, oz = 0;
-            if (amask) {
-                // candidate origin 1: the corner of the union of all active boxes
-                const int big = 0x7fffffff;
-                int ux = __reduce_min_sync(0xffffffffu, active ? bb.lo[0] : big) & ~(xalign - 1);
-                int uy = __reduce_min_sync(0xffffffffu, active ? bb.lo[1] : big);
-                int uz = __reduce_min_sync(0xffffffffu, active ? bb.lo[2] : big);
-                const unsigned fu = __ballot_sync(0xffffffffu, active && aabb_fits<BOX>(bb, ux, uy, uz));
-                // candidate origin 2: the first active matrix's own box (the centre probe in a registration loop)
-                const int src = __ffs(amask) - 1;
-                const int ax = __shfl_sync(0xffffffffu, bb.lo[0], src) & ~(xalign - 1);
-                const int ay = __shfl_sync(0xffffffffu, bb.lo[1], src);
-                const int az = __shfl_sync(0xffffffffu, bb.lo[2], src);
-                const unsigned fa = __ballot_sync(0xffffffffu, active && aabb_fits<BOX>(bb, ax, ay, az));
-                const bool use_union = __popc(fu) >= __popc(fa);
-                ox = use_union ? ux : ax; oy = use_union ? uy : ay; oz = use_union ? uz : az;
-                boxmask = use_union ? fu : fa;
-                if (active) mine = tile_place<BOX>(bb, ox, oy, oz);
-            }
-            if (lane == 0) mbar_wait<1000>(bar0 + 8 * (NST + s), ph ^ 1u);
-            __syncwarp();
-            if (lane < kMaxMulti) infos[s * kMaxMulti + lane] = mine;
-            __syncwarp();
-            if (lane == 0) {
-                if (boxmask) {
-                    mbar_arrive_expect_tx(bar0 + 8 * s, L::kBoxBytes);
-                    tma_load_3d(smem_u32(tsm + L::kStageBytes * s), &tmap, bar0 + 8 * s, ox, oy, oz);
-                } else {
-                    mbar_arrive(bar0 + 8 * s);
+            unsigned rem = __ballot_sync(0xffffffffu, active);       // matrices of this tile position still without a box
+            int nbox = 0;
+            do {
+                TileInfo mine;                                       // default: not in this stage (or outside) -> skipped
+                mine.rx = mine.ry = mine.rz = 0;
+                mine.bx = mine.by = mine.bz = 0;
+                mine.cls = kOutside;
+                unsigned boxmask = 0;
+                int ox = 0, oy = 0, oz = 0;
+                if (rem) {
+                    const bool inrem = (rem >> lane) & 1u;
+                    // candidate origin 1: the corner of the union of the remaining boxes
+                    const int big = 0x7fffffff;
+                    const int ux = __reduce_min_sync(0xffffffffu, inrem ? bb.lo[0] : big) & ~(xalign - 1);
+                    const int uy = __reduce_min_sync(0xffffffffu, inrem ? bb.lo[1] : big);
+                    const int uz = __reduce_min_sync(0xffffffffu, inrem ? bb.lo[2] : big);
+                    const unsigned fu = __ballot_sync(0xffffffffu, inrem && aabb_fits<BOX>(bb, ux, uy, uz));
+                    // candidate origin 2: the first remaining matrix's own box (the centre probe in a registration loop)
+                    const int src = __ffs(rem) - 1;
+                    const int ax = __shfl_sync(0xffffffffu, bb.lo[0], src) & ~(xalign - 1);
+                    const int ay = __shfl_sync(0xffffffffu, bb.lo[1], src);
+                    const int az = __shfl_sync(0xffffffffu, bb.lo[2], src);
+                    const unsigned fa = __ballot_sync(0xffffffffu, inrem && aabb_fits<BOX>(bb, ax, ay, az));
+                    const bool use_union = __popc(fu) >= __popc(fa);
+                    ox = use_union ? ux : ax; oy = use_union ? uy : ay; oz = use_union ? uz : az;
+                    boxmask = use_union ? fu : fa;
+                    // the last box of the position also carries whatever still does not fit (tile_place marks those
+                    // kNoFit: per-voxel gather); a matrix whose own tile is larger than the box ends the search
+                    const bool last_box = boxmask == 0u || nbox + 1 == kMultiBoxes || (rem & ~boxmask) == 0u;
+                    if (inrem && (last_box || ((boxmask >> lane) & 1u))) mine = tile_place<BOX>(bb, ox, oy, oz);
+                    rem = last_box ? 0u : (rem & ~boxmask);
                 }
-            }
+                if (lane == 0) mbar_wait<1000>(bar0 + 8 * (NST + s), ph ^ 1u);
+                __syncwarp();
+                if (lane < kMaxMulti) infos[s * kMaxMulti + lane] = mine;
+                if (lane == 0) s_hdr[s] = rem == 0u ? 1u : 0u;
+                __syncwarp();
+                if (lane == 0) {
+                    if (boxmask) {
+                        mbar_arrive_expect_tx(bar0 + 8 * s, L::kBoxBytes);
+                        tma_load_3d(smem_u32(tsm + L::kStageBytes * s), &tmap, bar0 + 8 * s, ox, oy, oz);
+                    } else {
+                        mbar_arrive(bar0 + 8 * s);
+                    }
+                }
+                if (++s == NST) { s = 0; ph ^= 1u; }
+                ++nbox;
+            } while (rem);
             advance();
-            if (++s == NST) { s = 0; ph ^= 1u; }
         }
     } else {
         // ---------------- consumers: G groups of 8 warps, every group against the same box ----------------
@@ -155,45 +180,45 @@ tile_multi_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constan
                 load_fixed<TF>(fv, fp, nk, plane);
             }
             unsigned mbits = 0xffu;
+            bool skip = false;
             if (MASK) {                                   // the mask of the tile position, shared by every matrix
                 const int i = i0 + lane, j = j0 + warp;
                 const int mk = (i < p.ox && j < p.oy) ? min(kTZ, p.oz - k0) : 0;
                 mbits = load_mask_bits(p.fmask + (((size_t)k0 * p.oy + j) * p.ox + i), mk, plane);
-                if (__all_sync(0xffffffffu, mbits == 0u)) {       // nothing of this warp's row is in the mask
-                    __syncwarp();
-                    mbar_wait<32>(bar0 + 8 * s, ph);
-                    if (lane == 0) mbar_arrive(bar0 + 8 * (NST + s));
-                    if (++s == NST) { s = 0; ph ^= 1u; }
-                    continue;
-                }
+                skip = __all_sync(0xffffffffu, mbits == 0u);     // nothing of this warp's row is in the mask
             }
-            mbar_wait<32>(bar0 + 8 * s, ph);
-            const unsigned char *stage = tsm + L::kStageBytes * s;
-            // group (grp + n) mod G starts at matrix 0: with 13 matrices and 2 groups the 7 / 6 split alternates
-            // from tile to tile and both groups do the same work over two tiles
-            for (int m = (grp + n) % G; m < n_mats; m += G) {
-                const TileInfo ti = infos[s * kMaxMulti + m];
-                if (ti.cls == kOutside) continue;                    // warp-uniform
-                double acc = 0.0;
-                unsigned cnt = 0;
-                if (ti.cls == kNoFit) {
-                    tile_compute_nobox<TM, TF, TM, kSsd, false, VTK>(p, s_A + 12 * m, ti.cls, i0, j0, k0, lane, warp, acc, cnt, nullptr);
-                } else {
-                    const ThreadGeom geom = make_thread_geom(s_A + 12 * m, lane, warp);
-                    if (ti.cls == kInterior)
-                        tile_compute<TM, TF, TM, kSsd, false, VTK, false, BOX, kFxKeep, MASK>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt,
-                                                                                        nullptr, fv, nullptr, 0, mbits);
-                    else
-                        tile_compute<TM, TF, TM, kSsd, false, VTK, true, BOX, kFxKeep, MASK>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt,
-                                                                                       nullptr, fv, nullptr, 0, mbits);
+            // one ring stage per box of this tile position (usually one); the header word says which is the last
+            unsigned last;
+            do {
+                mbar_wait<32>(bar0 + 8 * s, ph);
+                last = s_hdr[s];
+                const unsigned char *stage = tsm + L::kStageBytes * s;
+                // group (grp + n) mod G starts at matrix 0: with 13 matrices and 2 groups the 7 / 6 split alternates
+                // from tile to tile and both groups do the same work over two tiles
+                for (int m = (grp + n) % G; m < n_mats && !skip; m += G) {
+                    const TileInfo ti = infos[s * kMaxMulti + m];
+                    if (ti.cls == kOutside) continue;                    // warp-uniform: outside, or served by another stage
+                    double acc = 0.0;
+                    unsigned cnt = 0;
+                    if (ti.cls == kNoFit) {
+                        tile_compute_nobox<TM, TF, TM, kSsd, false, VTK>(p, s_A + 12 * m, ti.cls, i0, j0, k0, lane, warp, acc, cnt, nullptr);
+                    } else {
+                        const ThreadGeom geom = make_thread_geom(s_A + 12 * m, lane, warp);
+                        if (ti.cls == kInterior)
+                            tile_compute<TM, TF, TM, kSsd, false, VTK, false, BOX, kFxKeep, MASK>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt,
+                                                                                            nullptr, fv, nullptr, 0, mbits);
+                        else
+                            tile_compute<TM, TF, TM, kSsd, false, VTK, true, BOX, kFxKeep, MASK>(p, stage, ti, geom, i0, j0, k0, lane, warp, acc, cnt,
+                                                                                           nullptr, fv, nullptr, 0, mbits);
+                    }
+                    // per-thread accumulators in shared memory: nothing between two tiles waits on another lane
+                    g_acc[m * kMultiLanes] += acc;
+                    g_cnt[m * kMultiLanes] += cnt;
                 }
-                // per-thread accumulators in shared memory: nothing between two tiles waits on another lane
-                g_acc[m * kMultiLanes] += acc;
-                g_cnt[m * kMultiLanes] += cnt;
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar0 + 8 * (NST + s));
-            if (++s == NST) { s = 0; ph ^= 1u; }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar0 + 8 * (NST + s));
+                if (++s == NST) { s = 0; ph ^= 1u; }
+            } while (!last);
         }
     }
 

@@ -160,7 +160,8 @@ def _fixed_mask(mask, fixed):
     return m
 
 
-def resample_ssd(fixed, mov, A=None, d_A=None, mode="itk", ws=None, out=None, background=0.0, fixed_mask=None):
+def resample_ssd(fixed, mov, A=None, d_A=None, mode="itk", ws=None, out=None, background=0.0, fixed_mask=None,
+                 moving_mask=None):
     """Fused resample + SSD for n candidate matrices in one launch.  Returns (ssd[n] f64, count[n] i64)
     device tensors (views into ``ws``).  ``out`` (n == 1) also stores the resampled volume.  ``fixed_mask``
     (uint8 ``[z, y, x]`` on the fixed lattice): voxels where it is 0 take no part."""
@@ -171,10 +172,10 @@ def resample_ssd(fixed, mov, A=None, d_A=None, mode="itk", ws=None, out=None, ba
         ws = MetricWorkspace(mov.device, n_mats=n)
     if out is not None:
         out = _vol(out, "out")
-    fm = _fixed_mask(fixed_mask, fixed)
+    fm, mm = _fixed_mask(fixed_mask, fixed), _fixed_mask(moving_mask, mov)
     with torch.cuda.device(mov.device):
         check(lib.mia_resample_ssd_masked(mov.data_ptr(), _DT[mov.dtype], _dims(mov), fixed.data_ptr(), _DT[fixed.dtype],
-                                   fm.data_ptr() if fm is not None else None,
+                                   fm.data_ptr() if fm is not None else None, mm.data_ptr() if mm is not None else None,
                                    _dims(fixed), out.data_ptr() if out is not None else None,
                                    _DT[out.dtype] if out is not None else _DT[mov.dtype], n, Ah, Ad,
                                    float(background), _MODE[mode], ws.ssd.data_ptr(), ws.count.data_ptr(),
@@ -182,17 +183,19 @@ def resample_ssd(fixed, mov, A=None, d_A=None, mode="itk", ws=None, out=None, ba
     return ws.ssd[:n], ws.count[:n]
 
 
-def resample_jointhist(fixed, mov, frange, mrange, bins=64, A=None, d_A=None, mode="itk", ws=None, fixed_mask=None):
+def resample_jointhist(fixed, mov, frange, mrange, bins=64, A=None, d_A=None, mode="itk", ws=None, fixed_mask=None,
+                       moving_mask=None):
     """Fused resample + joint histogram.  Returns (hist[n, bins, bins] int32, count[n] i64) device tensors."""
     lib = _lib.load()
     fixed, mov = _vol(fixed, "fixed"), _vol(mov, "mov")
     n, Ah, Ad = _A_args(A, d_A)
     if ws is None or ws.n_mats < n or ws.bins != bins:
         ws = MetricWorkspace(mov.device, n_mats=n, bins=bins)
-    fm = _fixed_mask(fixed_mask, fixed)
+    fm, mm = _fixed_mask(fixed_mask, fixed), _fixed_mask(moving_mask, mov)
     with torch.cuda.device(mov.device):
         check(lib.mia_resample_jointhist_masked(mov.data_ptr(), _DT[mov.dtype], _dims(mov), fixed.data_ptr(),
                                          _DT[fixed.dtype], fm.data_ptr() if fm is not None else None,
+                                         mm.data_ptr() if mm is not None else None,
                                          _dims(fixed), n, Ah, Ad, _MODE[mode],
                                          float(frange[0]), float(frange[1]), float(mrange[0]), float(mrange[1]),
                                          int(bins), ws.hist.data_ptr(), ws.count.data_ptr(), ws.ws.data_ptr(),
@@ -200,7 +203,8 @@ def resample_jointhist(fixed, mov, frange, mrange, bins=64, A=None, d_A=None, mo
     return ws.hist[:n], ws.count[:n]
 
 
-def resample_mattes(fixed, mov, frange, mrange, bins=50, A=None, d_A=None, mode="itk", ws=None, fixed_mask=None):
+def resample_mattes(fixed, mov, frange, mrange, bins=50, A=None, d_A=None, mode="itk", ws=None, fixed_mask=None,
+                    moving_mask=None):
     """Fused resample + Mattes (Parzen-window) joint histogram.  Returns (hist[n, bins, bins] int64 in
     units of 1/1024 sample, count[n] i64) device tensors; ``mi_from_hist`` turns the histogram into MI."""
     lib = _lib.load()
@@ -208,10 +212,11 @@ def resample_mattes(fixed, mov, frange, mrange, bins=50, A=None, d_A=None, mode=
     n, Ah, Ad = _A_args(A, d_A)
     if ws is None or ws.n_mats < n or ws.bins != bins:
         ws = MetricWorkspace(mov.device, n_mats=n, bins=bins)
-    fm = _fixed_mask(fixed_mask, fixed)
+    fm, mm = _fixed_mask(fixed_mask, fixed), _fixed_mask(moving_mask, mov)
     with torch.cuda.device(mov.device):
         check(lib.mia_resample_mattes(mov.data_ptr(), _DT[mov.dtype], _dims(mov), fixed.data_ptr(), _DT[fixed.dtype],
-                                      fm.data_ptr() if fm is not None else None, _dims(fixed), n, Ah, Ad, _MODE[mode],
+                                      fm.data_ptr() if fm is not None else None,
+                                      mm.data_ptr() if mm is not None else None, _dims(fixed), n, Ah, Ad, _MODE[mode],
                                       float(frange[0]), float(frange[1]), float(mrange[0]), float(mrange[1]), int(bins),
                                       ws.hist64.data_ptr(), ws.count.data_ptr(), ws.ws.data_ptr(), ws.ws.numel(),
                                       _stream(mov)))

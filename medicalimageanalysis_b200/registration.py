@@ -39,6 +39,7 @@ class RegistrationConfig:
     mrange: tuple | None = None
     graph_iters: int = 10            # iterations captured per CUDA graph (0 = no graph)
     fixed_mask: object = None        # uint8 CUDA tensor on the fixed lattice (SetMetricFixedMask); None = all voxels
+    moving_mask: object = None       # same on the moving lattice (SetMetricMovingMask); runs the per-voxel kernel
 
 
 @dataclass
@@ -140,6 +141,9 @@ def register_rigid(fixed, moving, params0=None, cfg: RegistrationConfig | None =
     fmask = None
     if cfg.fixed_mask is not None:
         fmask = kernels._mask_u8(cfg.fixed_mask, fixed.array.shape, dev)      # converted once, outside the loop
+    mmask = None
+    if cfg.moving_mask is not None:
+        mmask = kernels._mask_u8(cfg.moving_mask, moving.array.shape, dev)
     if not is_ssd:
         frange = cfg.frange or _intensity_range(fixed.array)
         mrange = cfg.mrange or _intensity_range(moving.array)
@@ -155,11 +159,12 @@ def register_rigid(fixed, moving, params0=None, cfg: RegistrationConfig | None =
 
         def one_iteration():
             if is_ssd:
-                kernels.resample_ssd(fixed.array, moving.array, d_A=d_A, mode=cfg.mode, ws=ws, fixed_mask=fmask)
+                kernels.resample_ssd(fixed.array, moving.array, d_A=d_A, mode=cfg.mode, ws=ws, fixed_mask=fmask,
+                                     moving_mask=mmask)
                 metric = ws.ssd
             else:
                 kernels.resample_jointhist(fixed.array, moving.array, frange, mrange, bins=cfg.bins, d_A=d_A,
-                                           mode=cfg.mode, ws=ws, fixed_mask=fmask)
+                                           mode=cfg.mode, ws=ws, fixed_mask=fmask, moving_mask=mmask)
                 kernels.mi_from_hist(ws.hist, out=ws.mi)
                 metric = ws.mi
             _lib.check(lib.mia_optimizer_step(state.data_ptr(), metric.data_ptr(), ws.count.data_ptr(),
@@ -167,7 +172,7 @@ def register_rigid(fixed, moving, params0=None, cfg: RegistrationConfig | None =
 
         def one_iteration_mattes():
             kernels.resample_mattes(fixed.array, moving.array, frange, mrange, bins=cfg.bins, d_A=d_A, mode=cfg.mode,
-                                    ws=ws, fixed_mask=fmask)
+                                    ws=ws, fixed_mask=fmask, moving_mask=mmask)
             kernels.mi_from_hist(ws.hist64, out=ws.mi)
             metric = ws.mi
             _lib.check(lib.mia_optimizer_step(state.data_ptr(), metric.data_ptr(), ws.count.data_ptr(),
@@ -258,8 +263,13 @@ def register_rigid_multires(fixed, moving, params0=None, cfg: RegistrationConfig
             from . import kernels
             m8 = kernels._mask_u8(cfg.fixed_mask, fixed.array.shape, fixed.array.device)
             lmask = m8 if f == (1, 1, 1) else (kernels.shrink_mean((m8 != 0).float(), f) >= 0.5).to(m8.dtype)
+        lmov = None
+        if cfg.moving_mask is not None:
+            from . import kernels
+            mm8 = kernels._mask_u8(cfg.moving_mask, moving.array.shape, moving.array.device)
+            lmov = mm8 if f == (1, 1, 1) else (kernels.shrink_mean((mm8 != 0).float(), f) >= 0.5).to(mm8.dtype)
         lcfg = dataclasses.replace(cfg, iterations=int(n_it), frange=frange, mrange=mrange, graph_iters=gi,
-                                   fixed_mask=lmask)
+                                   fixed_mask=lmask, moving_mask=lmov)
         res = register_rigid(fl, ml, params0=params, cfg=lcfg, center=center)
         params = res.params
         evals += res.evaluations

@@ -18,7 +18,15 @@ from __future__ import annotations
 
 import numpy as np
 
-from .reslice import oracle_reslice
+from .reslice import continuous_index, oracle_reslice
+
+
+def _moving_mask_hits(moving_mask, A, odims):
+    """SetMetricMovingMask: the mask voxel nearest to the mapped point (floor(c + 0.5), clamped like the taps)."""
+    mm = np.asarray(moving_mask)
+    c = continuous_index(A, odims)
+    idx = [np.clip(np.floor(c[a] + 0.5).astype(np.int64), 0, mm.shape[2 - a] - 1) for a in range(3)]
+    return mm[idx[2], idx[1], idx[0]] > 0
 
 
 def bin_index(v, vmin, vmax, bins):
@@ -30,7 +38,7 @@ def bin_index(v, vmin, vmax, bins):
     return np.clip(b, 0, bins - 1).astype(np.int64)
 
 
-def oracle_ssd(fixed, mov, A, mode="itk", fixed_mask=None):
+def oracle_ssd(fixed, mov, A, mode="itk", fixed_mask=None, moving_mask=None):
     """(ssd float64, n_valid int).  ``fixed`` defines the output lattice ([z,y,x]); ``fixed_mask`` (same lattice):
     voxels where it is 0 take no part (SetMetricFixedMask, ``utils/deformable/simpleitk.py:116-117``)."""
     fixed = np.asarray(fixed)
@@ -38,18 +46,22 @@ def oracle_ssd(fixed, mov, A, mode="itk", fixed_mask=None):
     _, vals, mask = oracle_reslice(mov, A, odims, 0.0, mode, np.float32, return_float=True)
     if fixed_mask is not None:
         mask = mask & (np.asarray(fixed_mask) > 0)
+    if moving_mask is not None:
+        mask = mask & _moving_mask_hits(moving_mask, A, odims)
     d = fixed.astype(np.float64) - vals
     d = d[mask]
     return float(np.sum(d * d)), int(mask.sum())
 
 
-def oracle_joint_hist(fixed, mov, A, bins, frange, mrange, mode="itk", fixed_mask=None):
+def oracle_joint_hist(fixed, mov, A, bins, frange, mrange, mode="itk", fixed_mask=None, moving_mask=None):
     """(H uint64 [bins, bins] indexed [fixed_bin, moving_bin], n_valid)."""
     fixed = np.asarray(fixed)
     odims = (fixed.shape[2], fixed.shape[1], fixed.shape[0])
     _, vals, mask = oracle_reslice(mov, A, odims, 0.0, mode, np.float32, return_float=True)
     if fixed_mask is not None:
         mask = mask & (np.asarray(fixed_mask) > 0)
+    if moving_mask is not None:
+        mask = mask & _moving_mask_hits(moving_mask, A, odims)
     bf = bin_index(fixed[mask], frange[0], frange[1], bins)
     bm = bin_index(vals[mask].astype(np.float32), mrange[0], mrange[1], bins)
     H = np.bincount(bf * bins + bm, minlength=bins * bins).reshape(bins, bins).astype(np.uint64)
@@ -86,7 +98,7 @@ def parzen_table():
     return tab
 
 
-def oracle_mattes_hist(fixed, mov, A, bins, frange, mrange, mode="itk", fixed_mask=None):
+def oracle_mattes_hist(fixed, mov, A, bins, frange, mrange, mode="itk", fixed_mask=None, moving_mask=None):
     """(H uint64 [bins, bins] in units of 1/1024 sample, n_valid).  Structure of
     itk::MattesMutualInformationImageToImageMetricv4 (named at ``utils/deformable/simpleitk.py:155-156``): 2 padding
     bins per side, box window on the fixed image, cubic B-spline over 4 bins on the moving image; the spec of the
@@ -96,6 +108,8 @@ def oracle_mattes_hist(fixed, mov, A, bins, frange, mrange, mode="itk", fixed_ma
     _, vals, mask = oracle_reslice(mov, A, odims, 0.0, mode, np.float32, return_float=True)
     if fixed_mask is not None:
         mask = mask & (np.asarray(fixed_mask) > 0)
+    if moving_mask is not None:
+        mask = mask & _moving_mask_hits(moving_mask, A, odims)
     fb = bin_index(fixed[mask], frange[0], frange[1], bins - 4) + 2
     v = vals[mask].astype(np.float32)
     mscale = np.float32(bins - 4) / (np.float32(mrange[1]) - np.float32(mrange[0]))

@@ -112,3 +112,35 @@ def test_masked_registration_ignores_what_the_mask_hides(cuda_device):
     mr = rigid.register_rigid_multires(fi, mi, cfg=cfg, shrink_factors=(2, 1), iterations=(60, 60))
     assert np.abs(mr.params[:3] - gt[:3]).max() < 0.3 and np.abs(mr.params[3:] - gt[3:]).max() < 0.6
     Data.clear()
+
+
+@pytest.mark.parametrize("modality", ["CT", "MR"])
+def test_moving_mask_nearest_voxel_semantics(cuda_device, modality):
+    """SetMetricMovingMask: a sample counts when the moving-mask voxel nearest to its mapped point is set."""
+    g, fixed, moving, _ = pair(fdtype=modality, mdtype=modality)
+    A = mats(g, 1, seed=11)[0]
+    mm = _mask(moving.shape, "ellipsoid")
+    fm = _mask(fixed.shape, "random", seed=3)
+    f, mv = torch.from_numpy(fixed).to(cuda_device), torch.from_numpy(moving).to(cuda_device)
+    for fmask in (None, fm):
+        ssd, cnt = kernels.resample_ssd(f, mv, A=A, fixed_mask=fmask, moving_mask=mm)
+        assert _lib.load().mia_debug_last_path() == 0                                   # per-voxel kernel
+        want, n = metrics.oracle_ssd(fixed, moving, A, "itk", fixed_mask=fmask, moving_mask=mm)
+        # float32 local coordinates against float64: a mapped point within 1e-6 of a half-voxel plane may pick the
+        # neighbouring mask voxel
+        assert abs(int(cnt[0]) - n) <= max(4, 1e-5 * n)
+        assert abs(float(ssd[0]) - want) <= 1e-4 * want
+    fr, mr = (float(fixed.min()), float(fixed.max())), (float(moving.min()), float(moving.max()))
+    H, hc = kernels.resample_jointhist(f, mv, fr, mr, bins=32, A=A, moving_mask=mm)
+    Hw, nw = metrics.oracle_joint_hist(fixed, moving, A, 32, fr, mr, moving_mask=mm)
+    assert abs(int(hc[0]) - nw) <= 4 and np.abs(H[0].cpu().numpy().astype(np.int64) - Hw.astype(np.int64)).sum() <= 16
+    Hm, mc = kernels.resample_mattes(f, mv, fr, mr, bins=32, A=A, moving_mask=mm)
+    Hmw, nmw = metrics.oracle_mattes_hist(fixed, moving, A, 32, fr, mr, moving_mask=mm)
+    assert abs(int(mc[0]) - nmw) <= 4
+    assert np.abs(Hm[0].cpu().numpy().astype(np.int64) - Hmw.astype(np.int64)).sum() <= 3e-4 * Hmw.sum()
+    # all-ones moving mask == no moving mask on the same (per-voxel) kernel
+    ones = np.ones(moving.shape, np.uint8)
+    s1, c1 = kernels.resample_ssd(f, mv, A=A, moving_mask=ones)
+    s1, c1 = float(s1[0]), int(c1[0])
+    s0, c0 = kernels.resample_ssd(f, mv, A=A)
+    assert c1 == int(c0[0]) and abs(s1 - float(s0[0])) <= 1e-6 * s1                 # tile vs per-voxel arithmetic
