@@ -352,6 +352,9 @@ def extras(dev, torch, kernels, peak):
 
 
 def main():
+    # NCCL prints its version banner to STDOUT at NCCL_DEBUG=VERSION; the contract is ONE JSON line there
+    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
