@@ -123,6 +123,9 @@ __global__ void __launch_bounds__(kDvfThreads, MIA_DVF_MINB) warp_dvf_kernel(con
 #ifndef MIA_DVF_STAGED_MINB
 #define MIA_DVF_STAGED_MINB 3
 #endif
+#ifndef MIA_DVF_PREFETCH
+#define MIA_DVF_PREFETCH 0
+#endif
 // DIAG: B is diagonal (image axes along the physical axes, the usual case): one FFMA per axis instead of three.
 template <typename TM, typename TO, bool CLOSED, class BOX, bool DIAG>
 __global__ void __launch_bounds__(kDvfThreads, MIA_DVF_STAGED_MINB)
@@ -158,6 +161,39 @@ warp_dvf_tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
     unsigned phase = 0;
     const f32x2 magic2 = pk(kMagic, kMagic);
 
+    // The field of tile t + gridDim.x can be requested while tile t is computed (MIA_DVF_PREFETCH): of the two serial
+    // round trips per tile -- field, then box -- the first then overlaps the arithmetic of the previous tile.
+    // Measured and left OFF: the 24 extra live registers cost more than the overlap gains -- 3 CTAs of 80 registers
+    // spill (int16 410 -> 469 us), 2 CTAs of 128 registers lose the third CTA (442 us).
+    float d[kTZ][3];
+    auto fetch = [&](unsigned tt) {
+        if (tt >= ntiles) return;
+        const int tz = (int)(tt / (unsigned)(ntx * nty)), r2 = (int)(tt % (unsigned)(ntx * nty));
+        const int i = (r2 % ntx) * 32 + lane, j = (r2 / ntx) * 8 + warp, k0 = tz * kTZ;
+        const int kcnt = ((i < p.ox) & (j < p.oy)) ? min(kTZ, p.oz - k0) : 0;
+        const float *q = p.dvf + 3 * (((size_t)k0 * p.oy + j) * p.ox + i);
+        if (kcnt == kTZ) {                            // full column: no predicates, one stepped 64-bit pointer
+#pragma unroll
+            for (int kz = 0; kz < kTZ; ++kz) {        // all field loads in flight first
+                asm("" : "+l"(q));
+                d[kz][0] = __ldg(q);
+                d[kz][1] = __ldg(q + 1);
+                d[kz][2] = __ldg(q + 2);
+                q += 3u * plane;
+            }
+        } else {
+#pragma unroll
+            for (int kz = 0; kz < kTZ; ++kz) {
+                const bool live = kz < kcnt;
+                d[kz][0] = live ? __ldg(q) : 0.0f;
+                d[kz][1] = live ? __ldg(q + 1) : 0.0f;
+                d[kz][2] = live ? __ldg(q + 2) : 0.0f;
+                q += 3u * plane;
+            }
+        }
+    };
+    if (MIA_DVF_PREFETCH) fetch(blockIdx.x);
+
     for (unsigned t = blockIdx.x; t < ntiles; t += gridDim.x) {
         const int tz = (int)(t / (unsigned)(ntx * nty)), r2 = (int)(t % (unsigned)(ntx * nty));
         const int i = (r2 % ntx) * 32 + lane, j = (r2 / ntx) * 8 + warp, k0 = tz * kTZ;
@@ -181,27 +217,7 @@ warp_dvf_tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
         // numbers.  Border columns, partial z tiles and fields that leave the volume take the per-voxel path.
         float fmnx = INFINITY, fmny = INFINITY, fmnz = INFINITY, fmxx = -INFINITY, fmxy = -INFINITY, fmxz = -INFINITY;
         {
-            const float *q = p.dvf + 3 * v;
-            float d[kTZ][3];
-            if (kcnt == kTZ) {                            // full column: no predicates, one stepped 64-bit pointer
-#pragma unroll
-                for (int kz = 0; kz < kTZ; ++kz) {        // all field loads in flight first
-                    asm("" : "+l"(q));
-                    d[kz][0] = __ldg(q);
-                    d[kz][1] = __ldg(q + 1);
-                    d[kz][2] = __ldg(q + 2);
-                    q += 3u * plane;
-                }
-            } else {
-#pragma unroll
-                for (int kz = 0; kz < kTZ; ++kz) {
-                    const bool live = kz < kcnt;
-                    d[kz][0] = live ? __ldg(q) : 0.0f;
-                    d[kz][1] = live ? __ldg(q + 1) : 0.0f;
-                    d[kz][2] = live ? __ldg(q + 2) : 0.0f;
-                    q += 3u * plane;
-                }
-            }
+            if (!MIA_DVF_PREFETCH) fetch(t);
 #pragma unroll
             for (int kz = 0; kz < kTZ; ++kz) {
                 const float rx = fmaf((float)kz, a2x, r.fx), ry = fmaf((float)kz, a2y, r.fy), rz = fmaf((float)kz, a2z, r.fz);
@@ -265,6 +281,11 @@ warp_dvf_tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
         bx0 &= ~(xalign - 1);                                   // TMA: inner coordinate * element size = 0 mod 16 bytes
         const bool fits = !none && (bx1 + 2 - bx0 <= BOX::kX) && (by1 + 2 - by0 <= BOX::kY) && (bz1 + 2 - bz0 <= BOX::kZ);
         TO *o = out + v;
+        if (fits && threadIdx.x == 0) {
+            mbar_arrive_expect_tx(bar, kBoxBytes);
+            tma_load_3d(smem_u32(dsm), &tmap, bar, bx0, by0, bz0);
+        }
+        if (MIA_DVF_PREFETCH) fetch(t + gridDim.x);           // d[] is dead here: the coordinates are in lx / ly / lz
         if (none) {
 #pragma unroll
             for (int kz = 0; kz < kTZ; ++kz)
@@ -281,10 +302,6 @@ warp_dvf_tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
                 }
             }
         } else {
-            if (threadIdx.x == 0) {
-                mbar_arrive_expect_tx(bar, kBoxBytes);
-                tma_load_3d(smem_u32(dsm), &tmap, bar, bx0, by0, bz0);
-            }
             const int tbx = r.bx - bx0, tby = r.by - by0, tbz = r.bz - bz0;
             const uint32_t ubase = smem_u32(dsm) + (uint32_t)((tbz * BOX::kY + tby) * BOX::kX + tbx) * ES + p.magic_fold;
             // a voxel that is outside contributed nothing to the box, so it must not address beyond it either: its
