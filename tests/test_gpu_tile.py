@@ -246,3 +246,36 @@ def test_histogram_sizes_in_any_order(cuda_device):
         if bins in ref:
             assert torch.equal(h, ref[bins])
         ref[bins] = h.clone()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [np.int16, np.float32])
+def test_multi_matrix_kernel_groups_probes_into_several_boxes(cuda_device, dtype):
+    """A wide isotropic lattice (1024 x 1024 x 24 voxels of 0.5 mm): +-0.5 degree probes move the far tiles by +-4.5
+    voxels, so one box cannot serve all 13 matrices there and the producer opens a second / third box per tile
+    position (mia_tile_multi.cuh).  Every probe must equal its own one-matrix launch and the C/OpenMP oracle."""
+    import torch
+    from medicalimageanalysis_b200 import _lib, geometry as G, kernels
+    from medicalimageanalysis_b200.registration import probe_params
+    from oracle import native
+    shape, sp = (24, 1024, 1024), (0.5, 0.5, 0.5)
+    rng = np.random.default_rng(5)
+    z, y, x = np.meshgrid(np.arange(shape[0]), np.arange(shape[1]), np.arange(shape[2]), indexing="ij", sparse=True)
+    base = 600 * np.sin(x / 17.0) * np.cos(y / 23.0) * np.sin(z / 5.0 + 0.3)
+    fixed = (base + rng.normal(0, 10, shape)).astype(dtype)
+    moving = (600 * np.sin(x / 17.0 + 0.1) * np.cos(y / 23.0 - 0.05) * np.sin(z / 5.0 + 0.35)).astype(dtype)
+    g = G.Grid((shape[2], shape[1], shape[0]), sp, tuple(-0.5 * np.array(sp) * np.array(shape[::-1])))
+    p2w, w2p = G.index_to_physical(g), G.physical_to_index(g)
+    A = np.stack([(w2p @ G.params_to_matrix(p, np.zeros(3)) @ p2w)[:3]
+                  for p in probe_params(np.array([0.2, -0.1, 0.3, 0.4, -0.2, 0.1]), 1.0, np.array([0.5] * 6))])
+    f, m = torch.from_numpy(fixed).to(cuda_device), torch.from_numpy(moving).to(cuda_device)
+    s13, c13 = kernels.resample_ssd(f, m, A=A)
+    assert _lib.load().mia_debug_last_path() == 2
+    s13, c13 = s13.clone(), c13.clone()
+    for i in range(13):
+        s1, c1 = kernels.resample_ssd(f, m, A=A[i])
+        assert int(c1[0]) == int(c13[i]), i
+        assert abs(float(s1[0]) - float(s13[i])) <= 1e-7 * float(s13[i]), i      # gather-path tiles differ in the last bits
+    for i in (0, 1, 4, 6):                                                        # centre, +rx, -ry, -rz
+        want, n = native.reslice_ssd(fixed, moving, A[i], "itk")
+        assert abs(int(c13[i]) - n) <= max(4, 2e-6 * n) and abs(float(s13[i]) - want) <= 1e-5 * want
