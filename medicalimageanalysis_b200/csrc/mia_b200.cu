@@ -251,10 +251,9 @@ void fill_tile(KParams &p)
     p.ntiles = (long long)p.ntx * p.nty * ((p.oz + kTZ - 1) / kTZ);
 }
 
-template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, bool MASK = false>
+template <typename TM, typename TF, typename TO, int METRIC, bool STORE, bool VTK, bool MASK = false, class CFG = TileCfg<TM, METRIC>>
 int launch_tile(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream_t s)
 {
-    using CFG = TileCfg<TM, METRIC>;
     using BOX = typename CFG::BOX;
     constexpr int NST = CFG::NST, MINB = CFG::MINB;
     constexpr bool PREFETCH = CFG::PREFETCH;
@@ -295,12 +294,20 @@ int launch_tile(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream
 }
 
 
+// Second box family of the store kernel: rotations in the x-y plane beyond what the standard box takes (about 11 degrees
+// for int16).  A 32 x 8 x 8 tile turned by any in-plane angle spans at most 32 rows and 42 columns of the moving
+// volume, so a 36-row box serves every angle about z (with a few degrees of tilt); the per-voxel kernel remains for
+// large tilts.  This is the interactive view rotation (Image.update_rotation) and Rigid.update_rotation.
+template <typename TM> struct TallCfg;
+template <> struct TallCfg<int16_t> : TileCfgT<72, 35, 11, 2, 2, false> {};     // 54 KB per stage; 36-word pitch: a warp that runs down a box column (90 degrees) hits 8 banks, not 1
+template <> struct TallCfg<float> : TileCfgT<48, 36, 11, 2, 1, false> {};       // 76 KB per stage, one CTA per SM
+
 // One (element type, box) attempt: fit test for host matrices, tensor map, launch.
-template <int METRIC, bool STORE, typename TM>
+template <int METRIC, bool STORE, typename TM, class CFG = TileCfg<TM, METRIC>>
 int try_tile_box(int mode, const void *d_mov, const int mdims[3], const double *A_host, int n_mats, KParams p,
                  cudaStream_t s, bool &launched)
 {
-    using BOX = typename TileCfg<TM, METRIC>::BOX;
+    using BOX = typename CFG::BOX;
     launched = false;
     alignas(64) CUtensorMap map;
     for (int m = 0; A_host && m < n_mats; ++m)
@@ -314,14 +321,14 @@ int try_tile_box(int mode, const void *d_mov, const int mdims[3], const double *
         // masked metrics exist without a stored output only (SSD / joint histogram inside a registration loop)
         if constexpr (!STORE && METRIC != kNone) {
             launched = true;
-            return mode == MIA_MODE_VTK ? launch_tile<TM, TM, TM, METRIC, false, true, true>(map, p, n_mats, s)
-                                        : launch_tile<TM, TM, TM, METRIC, false, false, true>(map, p, n_mats, s);
+            return mode == MIA_MODE_VTK ? launch_tile<TM, TM, TM, METRIC, false, true, true, CFG>(map, p, n_mats, s)
+                                        : launch_tile<TM, TM, TM, METRIC, false, false, true, CFG>(map, p, n_mats, s);
         }
         return MIA_OK;
     }
     launched = true;
-    return mode == MIA_MODE_VTK ? launch_tile<TM, TM, TM, METRIC, STORE, true>(map, p, n_mats, s)
-                                : launch_tile<TM, TM, TM, METRIC, STORE, false>(map, p, n_mats, s);
+    return mode == MIA_MODE_VTK ? launch_tile<TM, TM, TM, METRIC, STORE, true, false, CFG>(map, p, n_mats, s)
+                                : launch_tile<TM, TM, TM, METRIC, STORE, false, false, CFG>(map, p, n_mats, s);
 }
 
 // Multi-matrix SSD (mia_tile_multi.cuh): one box per tile position for all matrices of the launch, one CTA per SM
@@ -469,8 +476,14 @@ int mia_resample_rigid(const void *d_mov, int mov_dtype, const int mdims[3], voi
     g_last_path = 0;
     if (mov_dtype == out_dtype) {
         bool launched = false;
-        const int rc = try_tile<kNone, true>(mov_dtype, mode, d_mov, mdims, A, 1, p, s, launched);
+        int rc = try_tile<kNone, true>(mov_dtype, mode, d_mov, mdims, A, 1, p, s, launched);
         if (launched) return rc;
+        rc = mov_dtype == MIA_F32 ? try_tile_box<kNone, true, float, TallCfg<float>>(mode, d_mov, mdims, A, 1, p, s, launched)
+                                  : try_tile_box<kNone, true, int16_t, TallCfg<int16_t>>(mode, d_mov, mdims, A, 1, p, s, launched);
+        if (launched) {
+            g_last_path = 4;
+            return rc;
+        }
     }
     if (mov_dtype == MIA_I16 && out_dtype == MIA_I16) launch_resample<int16_t, int16_t>(p, mode, grid, s);
     else if (mov_dtype == MIA_I16 && out_dtype == MIA_F32) launch_resample<int16_t, float>(p, mode, grid, s);

@@ -48,6 +48,11 @@ nvox = img.display.secondary_array.numel()
 res["n2_offaxis_update_rotation"] = {"us": round(us, 1), "out_shape": list(img.display.secondary_array.shape),
                                      "gvoxel_s": round(nvox / us / 1e3, 1)}
 
+for ang in (30, 60, 90):                                   # beyond the standard box: the tall-box family of the store kernel
+    us = timed(lambda: img.update_rotation(0, 0, ang))
+    res["n2_offaxis_update_rotation_z%d" % ang] = {"us": round(us, 1), "gvoxel_s": round(img.display.secondary_array.numel() / us / 1e3, 1)}
+img.reset_array()
+
 # N3: dose on the CT lattice under a mask
 dshape, dsp = (150, 200, 200), (2.5, 2.5, 5.0)
 dz, dy, dx = (torch.linspace(-1, 1, n, device=dev) for n in dshape)
