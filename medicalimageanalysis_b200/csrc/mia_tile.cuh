@@ -460,7 +460,18 @@ __device__ __forceinline__ void tile_compute(const KParams &p, const unsigned ch
         static_assert(!(MASK && STORE), "a masked metric does not store (the mask would punch holes in the output)");
         if (STORE) {
             // one 64-bit output pointer stepped by the plane pitch: 2 address instructions per store, not 5
-            const TO o0 = tile_to_out<TO, VTK>(val0), o1 = tile_to_out<TO, VTK>(val1);
+            TO o0, o1;
+            if (sizeof(TO) == 2 && sizeof(TM) == 2 && VTK) {
+                // int16 in, int16 out, floor(v + 0.5): the interpolant of int16 taps stays inside the int16 range
+                // (convex weights; the float32 lerp overshoots by an ulp at most), so the saturating F2I (quarter-rate
+                // XU, one per voxel) is not needed: floor through the mantissa for the pair, low 16 bits are the result
+                const f32x2 r2 = add2_rm(add2(val2, pk(0.5f, 0.5f)), magic2);
+                o0 = (TO)(short)(unsigned short)(uint32_t)r2;
+                o1 = (TO)(short)(unsigned short)(uint32_t)(r2 >> 32);
+            } else {
+                o0 = tile_to_out<TO, VTK>(val0);
+                o1 = tile_to_out<TO, VTK>(val1);
+            }
             asm("" : "+l"(out));
             if (live0) st_out(out, in0 ? o0 : bgv);
             out += plane;
