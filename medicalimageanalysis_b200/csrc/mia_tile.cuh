@@ -460,6 +460,8 @@ __device__ __forceinline__ void tile_compute(const KParams &p, const unsigned ch
         static_assert(!(MASK && STORE), "a masked metric does not store (the mask would punch holes in the output)");
         if (STORE) {
             // one 64-bit output pointer stepped by the plane pitch: 2 address instructions per store, not 5
+            // (one mad.wide.u32 per store -- plane bytes x constant plane number + base -- was measured slower:
+            // 230.0 against 225.6 us on C2)
             TO o0, o1;
             if (sizeof(TO) == 2 && sizeof(TM) == 2 && VTK) {
                 // int16 in, int16 out, floor(v + 0.5): the interpolant of int16 taps stays inside the int16 range
