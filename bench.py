@@ -246,7 +246,7 @@ def run_reference(args, rank):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_JSON_OUT, flush=True)
 
 
 def extras(dev, torch, kernels, peak):
@@ -351,10 +351,17 @@ def extras(dev, torch, kernels, peak):
     return out
 
 
+_JSON_OUT = sys.stdout
+
+
 def main():
-    # NCCL prints its version banner to STDOUT at NCCL_DEBUG=VERSION; the contract is ONE JSON line there
-    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-        os.environ["NCCL_DEBUG"] = "WARN"
+    # The contract is ONE JSON line on stdout, but NCCL writes its version banner there (neither NCCL_DEBUG nor
+    # NCCL_DEBUG_FILE moved it on this image): file descriptor 1 is pointed at stderr for every library, and the JSON
+    # line goes out through a private duplicate of the original stdout.
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -504,7 +511,7 @@ def main():
             line.setdefault("extra", {})["c5_sharded_register_ssd"] = sharded
         if probe_par is not None:
             line.setdefault("extra", {})["c3_probe_parallel_mi"] = probe_par
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_JSON_OUT, flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
