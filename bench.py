@@ -176,6 +176,58 @@ def sharded_registration_extra(torch, dev, world, peak):
             "note": "fixed lattice sharded by z-slab, moving replicated, all_reduce(SUM) of {ssd,count}[13] per iteration"}
 
 
+def batch_extra(torch, dev, world, rank, peak):
+    """Config 4: 16 CT volumes 512x512x300, each resampled through its own rigid matrix with the SSD against its fixed
+    volume fused into the same launch (6 algorithmic bytes per voxel); sharded by VOLUME over the ranks, no data-path
+    collective -- only the 16 {ssd, count} pairs are gathered.  Collective call: every rank runs it."""
+    from medicalimageanalysis_b200 import kernels
+    nvol = 16
+    mine = [v for v in range(nvol) if v % world == rank]
+    g = G.Grid((SHAPE[2], SHAPE[1], SHAPE[0]), SPACING, tuple(-0.5 * np.array(SPACING) * np.array(SHAPE[::-1])))
+    z, y, x = (torch.arange(n, device=dev, dtype=torch.float32) for n in SHAPE)
+    pairs, mats = [], []
+    for v in mine:                                                     # device-side synthesis, seeds 100 + v / 1000 + v
+        f = (600 * torch.sin(x[None, None, :] / (17 + v % 5)) * torch.cos(y[None, :, None] / 23) * torch.sin(z[:, None, None] / 19) + 10 * v).to(torch.int16)
+        m = (600 * torch.sin(x[None, None, :] / (17 + v % 5) + 0.1) * torch.cos(y[None, :, None] / 23) * torch.sin(z[:, None, None] / 19 + 0.05) + 10 * v).to(torch.int16)
+        rng = np.random.default_rng(1000 + v)
+        prm = np.concatenate([rng.uniform(-5, 5, 3), rng.uniform(-10, 10, 3)])
+        pairs.append((f, m, torch.empty_like(m)))
+        mats.append(G.compose_index_matrix(g, g, G.params_to_matrix(prm, (0.0, 0.0, 0.0))))
+    ws = kernels.MetricWorkspace(dev, n_mats=1)
+    res = torch.zeros((nvol, 2), dtype=torch.float64, device=dev)
+
+    def run_all():
+        for v, (f, m, o), A in zip(mine, pairs, mats):
+            s, c = kernels.resample_ssd(f, m, A=A, mode="itk", ws=ws, out=o)
+            res[v, 0] = s[0]
+            res[v, 1] = c[0].to(torch.float64)
+    run_all()
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    reps = 3
+    e0.record()
+    for _ in range(reps):
+        run_all()
+    e1.record()
+    torch.cuda.synchronize(dev)
+    t = torch.tensor([e0.elapsed_time(e1) * 1e-3 / reps], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(res, op=dist.ReduceOp.SUM)                    # every rank filled only its own rows
+    dt = float(t[0])
+    nv = nvol * SHAPE[0] * SHAPE[1] * SHAPE[2]
+    out = {"volumes": nvol, "n_gpus": world, "ms_per_batch": dt * 1e3, "gvoxel_s": nv / dt / 1e9,
+           "hbm_frac_per_gpu": 6.0 * nv / dt / 1e9 / peak / world,
+           "mse_first_last": [float(res[0, 0] / res[0, 1]), float(res[nvol - 1, 0] / res[nvol - 1, 1])],
+           "note": "sharded by volume, resample + SSD with store in one launch per volume, 16 {ssd,count} pairs gathered"}
+    del pairs
+    torch.cuda.empty_cache()
+    return out
+
+
 def probe_parallel_extra(torch, dev, world):
     """Config 3 (256^3 float32 CT -> MR, 64-bin MI, 200 iterations) with the 13 probes of every iteration dealt
     out over the ranks (the volume is too small for z-slabs).  Collective: every rank calls it."""
@@ -456,7 +508,7 @@ def main():
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)
     total_ms, e2e_s = float(tm[0]), float(tm[1])
 
-    sharded = probe_par = None
+    sharded = probe_par = batch = None
     if not args.no_extra:
         del movs, outs
         movs = outs = None
@@ -470,6 +522,10 @@ def main():
                 probe_par = probe_parallel_extra(torch, dev, world)
             except Exception as exc:
                 probe_par = {"error": repr(exc)}
+        try:
+            batch = batch_extra(torch, dev, world, rank, peak)
+        except Exception as exc:
+            batch = {"error": repr(exc)}
 
     if rank == 0:
         value = world * nvox_out * K / (total_ms * 1e-3) / 1e9
@@ -511,6 +567,8 @@ def main():
             line.setdefault("extra", {})["c5_sharded_register_ssd"] = sharded
         if probe_par is not None:
             line.setdefault("extra", {})["c3_probe_parallel_mi"] = probe_par
+        if batch is not None:
+            line.setdefault("extra", {})["c4_batch16_resample_ssd"] = batch
         print(json.dumps(line), file=_JSON_OUT, flush=True)
     if world > 1:
         dist.barrier()
