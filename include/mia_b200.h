@@ -250,6 +250,24 @@ int mia_resample_mattes(const void *d_mov, int mov_dtype, const int mdims[3], co
                         size_t ws_bytes, void *stream);
 int mia_mi_from_hist64(const unsigned long long *d_hist, int bins, int n_mats, double *d_mi, void *stream);
 
+/*
+ * mia_resample_ssd without any caller workspace and without any allocation.  This entry point has NO counterpart in
+ * the reference: it was added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  Arguments and results are those of
+ * mia_resample_ssd minus d_ws / ws_bytes; the scratch (staged matrices, per-block partials, tickets) is a file-scope
+ * device array of MIA_STATIC_WS_BYTES that every GPU which loads the library holds until exit.  Limit: n_mats <=
+ * MIA_STATIC_MAX_MATS, anything larger is rejected with MIA_ERR_ARG.  The call makes no cudaMalloc / cudaFree.
+ * All calls on a device share the array and it keeps the last call's contents (what must start at zero is cleared
+ * on `stream` by the call): calls of one process that overlap on the GPU (different streams or threads)
+ * race; serialise them on one stream.
+ */
+#define MIA_STATIC_MAX_MATS 16
+#define MIA_STATIC_WS_BYTES (512 * 1024)
+int mia_resample_ssd_static(const void *d_mov, int mov_dtype, const int mdims[3], const void *d_fixed,
+                            int fixed_dtype, const int odims[3], void *d_out, int out_dtype, int n_mats,
+                            const double *A, const double *d_A, double background, int mode, double *d_ssd,
+                            unsigned long long *d_count, void *stream);
+
 /* Page-locked host buffers for the *_host entry point (a NumPy array can wrap them). */
 void *mia_host_alloc(size_t bytes);
 int mia_host_free(void *p);

@@ -15,6 +15,7 @@ LIB_PATH = os.environ.get("MIA_B200_LIB") or os.path.join(_HERE, "libmia_b200.so
 MIA_I16, MIA_F32 = 0, 1
 MIA_MODE_VTK, MIA_MODE_ITK = 0, 1
 MIA_MAX_MATS, MIA_MAX_BINS = 32, 128
+MIA_STATIC_MAX_MATS, MIA_STATIC_WS_BYTES = 16, 512 * 1024
 
 _c = ctypes
 _vp, _i, _d, _f, _sz = _c.c_void_p, _c.c_int, _c.c_double, _c.c_float, _c.c_size_t
@@ -31,6 +32,7 @@ SIGNATURES = {
     "mia_permute_axes": (_i, [_vp, _i, _ip, _vp, _ip, _ip, _vp]),
     "mia_metric_workspace_bytes": (_sz, [_ip, _i, _i]),
     "mia_resample_ssd": (_i, [_vp, _i, _ip, _vp, _i, _ip, _vp, _i, _i, _dp, _vp, _d, _i, _vp, _vp, _vp, _sz, _vp]),
+    "mia_resample_ssd_static": (_i, [_vp, _i, _ip, _vp, _i, _ip, _vp, _i, _i, _dp, _vp, _d, _i, _vp, _vp, _vp]),
     "mia_resample_jointhist": (_i, [_vp, _i, _ip, _vp, _i, _ip, _i, _dp, _vp, _i, _f, _f, _f, _f, _i, _vp, _vp,
                                     _vp, _sz, _vp]),
     "mia_resample_ssd_masked": (_i, [_vp, _i, _ip, _vp, _i, _vp, _vp, _ip, _vp, _i, _i, _dp, _vp, _d, _i, _vp, _vp, _vp,

@@ -706,6 +706,58 @@ int mia_resample_mattes(const void *d_mov, int mov_dtype, const int mdims[3], co
 
 }  // extern "C"
 
+// ------------------------------------------------------------------------------------------------
+// mia_resample_ssd_static: the fused resample + SSD launch for callers that cannot allocate device memory
+// (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The metric workspace (staged matrices, per-block partials, tickets)
+// lives in a file-scope device array; every GPU that loads the library holds MIA_STATIC_WS_BYTES of it until exit.
+// All calls on one device share it: it keeps the previous call's contents (the tickets are cleared per call on the
+// caller's stream, nothing else needs to start at zero), and two calls that overlap on the GPU race.
+namespace {
+
+__device__ __align__(256) unsigned char g_static_metric_ws[MIA_STATIC_WS_BYTES];
+
+// In host code the array's name is a host-side stand-in, not a device address: ask the runtime for the address once
+// per device, with that device current.
+int static_metric_ws(void **ptr)
+{
+    static std::mutex mu;
+    static void *cached[64] = {nullptr};
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(MIA_ERR_UNSUPPORTED, "mia_resample_ssd_static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!cached[dev]) {
+        void *p = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress(&p, g_static_metric_ws));
+        if (!p) return fail(MIA_ERR_CUDA, "mia_resample_ssd_static: cudaGetSymbolAddress returned a null address");
+        cached[dev] = p;
+    }
+    *ptr = cached[dev];
+    return MIA_OK;
+}
+
+}  // namespace
+
+extern "C" int mia_resample_ssd_static(const void *d_mov, int mov_dtype, const int mdims[3], const void *d_fixed,
+                                       int fixed_dtype, const int odims[3], void *d_out, int out_dtype, int n_mats,
+                                       const double *A, const double *d_A, double background, int mode, double *d_ssd,
+                                       unsigned long long *d_count, void *stream)
+{
+    if (n_mats < 1 || n_mats > MIA_STATIC_MAX_MATS)
+        return fail(MIA_ERR_ARG, "mia_resample_ssd_static: n_mats must be 1..%d (the static scratch holds %d bytes)",
+                    MIA_STATIC_MAX_MATS, MIA_STATIC_WS_BYTES);
+    const size_t need = ws_layout(n_mats).total;
+    if (need > (size_t)MIA_STATIC_WS_BYTES)
+        return fail(MIA_ERR_WORKSPACE, "mia_resample_ssd_static: %d matrices need %zu bytes of scratch, the static array holds %d",
+                    n_mats, need, MIA_STATIC_WS_BYTES);
+    void *ws = nullptr;
+    const int rc = static_metric_ws(&ws);
+    if (rc) return rc;
+    return mia_resample_ssd_masked(d_mov, mov_dtype, mdims, d_fixed, fixed_dtype, nullptr, nullptr, odims, d_out, out_dtype,
+                                   n_mats, A, d_A, background, mode, d_ssd, d_count, ws, (size_t)MIA_STATIC_WS_BYTES, stream);
+}
+
 #include "mia_host_api.inl"
 #include "mia_dvf.inl"
 #include "mia_dose.inl"
