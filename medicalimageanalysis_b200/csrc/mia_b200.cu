@@ -16,6 +16,7 @@
 #include "mia_optimizer.cuh"
 #include "mia_tile.cuh"
 #include "mia_tile_multi.cuh"
+#include "mia_tile_x2.cuh"
 #include "mia_dvf.cuh"
 #include "mia_dose.cuh"
 #include "mia_pyramid.cuh"
@@ -433,6 +434,98 @@ int try_multi(int dtype, int mode, const void *d_mov, const int mdims[3], const 
     return try_multi_t<int16_t>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
 }
 
+// ------------------------------------------------------------------------------------------------
+// x-pair tile kernel for int16 volumes (mia_tile_x2.cuh): 64 x 8 x 8 tiles, box 128 x 16 x 12 (48 KB per stage).
+// (box, ring depth, resident CTAs per SM); tuning builds override with -D.
+#ifndef MIA_X2_BY
+#define MIA_X2_BY 16
+#endif
+#ifndef MIA_X2_BZ
+#define MIA_X2_BZ 12
+#endif
+#ifndef MIA_X2_NST
+#define MIA_X2_NST 2
+#endif
+#ifndef MIA_X2_MINB
+#define MIA_X2_MINB 2
+#endif
+#define MIA_X2_CFG 128, MIA_X2_BY, MIA_X2_BZ, MIA_X2_NST, MIA_X2_MINB
+template <int BX, int BY, int BZ, int NST_, int MINB_>
+struct X2CfgT {
+    using BOX = Box<BX, BY, BZ>;
+    static constexpr int NST = NST_, MINB = MINB_;
+};
+using X2Cfg = X2CfgT<MIA_X2_CFG>;
+
+bool x2_path_disabled()
+{
+    static const bool off = [] { const char *e = getenv("MIA_NO_X2"); return e && *e && *e != '0'; }();
+    return off;
+}
+
+template <class BOX>
+bool x2_box_fits(const double *A)
+{
+    const Reach r = tile_reach_ext(A, kXW - 1, kXH - 1, kXD - 1);
+    const int B[3] = {BOX::kX, BOX::kY, BOX::kZ};
+    for (int a = 0; a < 3; ++a)
+        if (std::ceil(r.pos[a] - r.neg[a]) + 3.0 + (a == 0 ? 7.0 : 0.0) > (double)B[a]) return false;
+    return true;
+}
+
+template <bool VTK>
+int launch_x2(const CUtensorMap &map, const KParams &p, cudaStream_t s)
+{
+    using BOX = X2Cfg::BOX;
+    constexpr int NST = X2Cfg::NST, MINB = X2Cfg::MINB;
+    auto k = tile_x2_kernel<VTK, BOX, NST, MINB>;
+    const size_t smem = X2Smem<BOX, NST>::kBytes;
+    static std::mutex mu;
+    static std::map<int, int> occ;                         // device -> resident CTAs per SM
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    int nb = 0;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        auto it = occ.find(dev);
+        if (it == occ.end()) {
+            CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k, kX2Threads, smem));
+            if (nb < 1) return fail(MIA_ERR_UNSUPPORTED, "x-pair tile kernel does not fit on this device (%zu B smem)", smem);
+            occ[dev] = nb;
+        } else {
+            nb = it->second;
+        }
+    }
+    static const int maxb = [] { const char *e = getenv("MIA_X2_MAXB"); return e && *e ? atoi(e) : 0; }();   // tuning knob
+    if (maxb > 0 && nb > maxb) nb = maxb;
+    long long gx = (long long)sm_count() * nb;
+    if (gx > p.ntiles) gx = p.ntiles;
+    if (gx > kMaxGridX) gx = kMaxGridX;
+    k<<<dim3((unsigned)gx, 1, 1), kX2Threads, smem, s>>>(map, p);
+    CUDA_TRY(cudaGetLastError());
+    g_last_path = 5;
+    return MIA_OK;
+}
+
+// Pure resample, int16 in and out.  The host matrix is fit-tested against the box; anything else takes the older paths.
+int try_x2(int mode, const void *d_mov, const int mdims[3], const double *A_host, KParams p, cudaStream_t s, bool &launched)
+{
+    using BOX = X2Cfg::BOX;
+    launched = false;
+    if (tile_path_disabled() || x2_path_disabled() || !A_host || !x2_box_fits<BOX>(A_host)) return MIA_OK;
+    alignas(64) CUtensorMap map;
+    if (!make_tensor_map<int16_t, BOX>(&map, d_mov, mdims)) return MIA_OK;
+    p.ntx = (p.ox + kXW - 1) / kXW;
+    p.nty = (p.oy + kXH - 1) / kXH;
+    p.ntiles = (long long)p.ntx * p.nty * ((p.oz + kXD - 1) / kXD);
+    p.magic_fold = 0u - kMagicBits * (unsigned)((BOX::kY + 1) * BOX::kX + 1) * 2u;
+    if (p.ntiles > 0x7fffffffLL) return MIA_OK;
+    if ((long long)p.ox * p.oy * kXD >= 0x7fffffffLL) return MIA_OK;   // in-tile plane offsets are 32-bit
+    launched = true;
+    return mode == MIA_MODE_VTK ? launch_x2<true>(map, p, s) : launch_x2<false>(map, p, s);
+}
+
 // Try the tile path for (dtype, mode); `launched` tells whether it took the call.  A_host may be null
 // (device matrices: the kernel classifies every tile itself and falls back per tile).
 template <int METRIC, bool STORE>
@@ -476,7 +569,12 @@ int mia_resample_rigid(const void *d_mov, int mov_dtype, const int mdims[3], voi
     g_last_path = 0;
     if (mov_dtype == out_dtype) {
         bool launched = false;
-        int rc = try_tile<kNone, true>(mov_dtype, mode, d_mov, mdims, A, 1, p, s, launched);
+        int rc = MIA_OK;
+        if (mov_dtype == MIA_I16) {
+            rc = try_x2(mode, d_mov, mdims, A, p, s, launched);
+            if (launched) return rc;
+        }
+        rc = try_tile<kNone, true>(mov_dtype, mode, d_mov, mdims, A, 1, p, s, launched);
         if (launched) return rc;
         rc = mov_dtype == MIA_F32 ? try_tile_box<kNone, true, float, TallCfg<float>>(mode, d_mov, mdims, A, 1, p, s, launched)
                                   : try_tile_box<kNone, true, int16_t, TallCfg<int16_t>>(mode, d_mov, mdims, A, 1, p, s, launched);

@@ -1,0 +1,70 @@
+"""Kernel development probe: times the C2 resample (and C1 SSD) through the C ABI, prints the path taken and a hash of the
+output so that two builds / two paths (MIA_NO_X2=1) can be compared bit for bit."""
+import hashlib
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench                                                   # noqa: E402
+from medicalimageanalysis_b200 import _lib, geometry as G, kernels  # noqa: E402
+from medicalimageanalysis_b200.phantom import make_phantom      # noqa: E402
+
+
+def timeit(fn, n=20, warm=5):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n)]
+    for i, (a, b) in enumerate(ev):
+        a.record(); fn(); b.record()
+    torch.cuda.synchronize()
+    t = sorted(a.elapsed_time(b) for a, b in ev)
+    return {"us_med": 1e3 * t[len(t) // 2], "us_min": 1e3 * t[0]}
+
+
+def main():
+    dev = torch.device("cuda:0")
+    lib = _lib.load()
+    out = {"env_no_x2": os.environ.get("MIA_NO_X2", "")}
+    grid, A, dims = bench.workload_geometry()
+    oshape = (dims[2], dims[1], dims[0])
+    mov_h = make_phantom(bench.SHAPE, "CT", seed=2, spacing=bench.SPACING)
+    movs = [torch.from_numpy(mov_h).to(dev) for _ in range(3)]
+    outs = [torch.empty(oshape, dtype=torch.int16, device=dev) for _ in range(3)]
+    st = {"i": 0}
+
+    def c2():
+        i = st["i"] = (st["i"] + 1) % 3
+        kernels.resample(movs[i], A, oshape, background=-3001.0, mode="vtk", out=outs[i])
+    r = timeit(c2)
+    r["path"] = int(lib.mia_debug_last_path())
+    r["sha"] = hashlib.sha1(outs[0].cpu().numpy().tobytes()).hexdigest()[:16]
+    r["gvoxel_s"] = dims[0] * dims[1] * dims[2] / r["us_med"] / 1e3
+    r["frac"] = (2.0 * mov_h.size + 2.0 * dims[0] * dims[1] * dims[2]) / (r["us_med"] * 1e-6) / 1e9 / bench.measured_peak()[0]
+    out["c2_store_vtk"] = r
+    # ITK mode onto the fixed lattice (C4 flavour) with SSD + store, and SSD evaluate
+    g1 = G.Grid((512, 512, 300), bench.SPACING, tuple(-0.5 * np.array(bench.SPACING) * np.array(bench.SHAPE[::-1])))
+    M = G.params_to_matrix(bench.GT, (0.0, 0.0, 0.0))
+    A1 = G.compose_index_matrix(g1, g1, M)
+    fixed = torch.from_numpy(make_phantom(bench.SHAPE, "CT", seed=2, spacing=bench.SPACING, world_matrix=M)).to(dev)
+    ws = kernels.MetricWorkspace(dev, n_mats=1)
+    o = torch.empty_like(movs[0])
+    r = timeit(lambda: kernels.resample_ssd(fixed, movs[0], A=A1, mode="itk", ws=ws, out=o))
+    s, c = kernels.resample_ssd(fixed, movs[0], A=A1, mode="itk", ws=ws, out=o)
+    r.update(path=int(lib.mia_debug_last_path()), ssd=float(s[0]), count=int(c[0]),
+             sha=hashlib.sha1(o.cpu().numpy().tobytes()).hexdigest()[:16])
+    out["c2_ssd_store_itk"] = r
+    r = timeit(lambda: kernels.resample_ssd(fixed, movs[0], A=A1, mode="itk", ws=ws))
+    s, c = kernels.resample_ssd(fixed, movs[0], A=A1, mode="itk", ws=ws)
+    r.update(path=int(lib.mia_debug_last_path()), ssd=float(s[0]), count=int(c[0]))
+    out["c2_ssd_eval_itk"] = r
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()
