@@ -132,6 +132,18 @@ int mia_optimizer_init(void *d_state, const double params0[6], const double cent
                        double trans_step_mm, double min_step_scale, int maximize, double *d_A, void *stream);
 int mia_optimizer_step(void *d_state, const double *d_metric, const unsigned long long *d_count,
                        int metric_is_ssd, double *d_A, void *stream);
+/*
+ * The same step for the sharded loops (z-slabs of one large pair, or the 13 probes dealt out over the ranks).
+ * mia_metric_pack gathers this rank's partial results into ONE float64 buffer d_packed[2 * n_total]:
+ * [0, n_total) the metric and [n_total, 2 n_total) the voxel counts as float64 (exact below 2^53), both zero outside
+ * the rank's share [q0, q0 + n_local) -- so a single all-reduce(SUM) of 2 * n_total doubles per iteration combines the
+ * ranks.  mia_optimizer_step_packed then reads that buffer (n_total = 13) and, when d_A_slab != NULL, also writes the
+ * probe matrices shifted to the z-slab that starts at fixed plane k0 (A[:, 3] += A[:, 2] * k0).
+ */
+int mia_metric_pack(const double *d_metric, const unsigned long long *d_count, int n_local, int q0, int n_total,
+                    double *d_packed, void *stream);
+int mia_optimizer_step_packed(void *d_state, const double *d_packed, int metric_is_ssd, double *d_A, double *d_A_slab,
+                              int k0, void *stream);
 /* Copy the optimiser state back (synchronises `stream`).  Any output pointer may be NULL; hist_* hold
  * min(iters, max_hist) entries: the centre cost, parameters [n][6] and step scale seen at each step. */
 int mia_optimizer_read(const void *d_state, double params[6], double *scale, int *iters, int *converged,
@@ -268,9 +280,13 @@ int mia_resample_ssd_static(const void *d_mov, int mov_dtype, const int mdims[3]
                             const double *A, const double *d_A, double background, int mode, double *d_ssd,
                             unsigned long long *d_count, void *stream);
 
-/* Page-locked host buffers for the *_host entry point (a NumPy array can wrap them). */
+/* Page-locked host buffers for the *_host entry point (a NumPy array can wrap them).  mia_host_register pins memory the
+ * caller already owns -- e.g. its z-slab of ONE volume in a shared mapping that several ranks resample together
+ * (Rigid.create_image on a volume cut over the GPUs of a box, structure/rigid.py:646-695). */
 void *mia_host_alloc(size_t bytes);
 int mia_host_free(void *p);
+int mia_host_register(void *p, size_t bytes);
+int mia_host_unregister(void *p);
 
 #ifdef __cplusplus
 }

@@ -58,6 +58,10 @@ SIGNATURES = {
     "mia_read_file_to_device": (_i, [_c.c_char_p, _c.c_ulonglong, _c.c_ulonglong, _vp, _i]),
     "mia_write_file_from_device": (_i, [_c.c_char_p, _c.c_ulonglong, _vp, _c.c_ulonglong, _i, _i]),
     "mia_shrink_mean": (_i, [_vp, _i, _ip, _vp, _ip, _vp]),
+    "mia_metric_pack": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
+    "mia_optimizer_step_packed": (_i, [_vp, _vp, _i, _vp, _vp, _i, _vp]),
+    "mia_host_register": (_i, [_vp, _sz]),
+    "mia_host_unregister": (_i, [_vp]),
     "mia_host_alloc": (_vp, [_sz]),
     "mia_host_free": (_i, [_vp]),
 }

@@ -180,8 +180,29 @@ int mia_optimizer_step(void *d_state, const double *d_metric, const unsigned lon
 {
     if (!d_state || !d_metric || !d_A) return fail(MIA_ERR_ARG, "mia_optimizer_step: null pointer");
     if (metric_is_ssd && !d_count) return fail(MIA_ERR_ARG, "mia_optimizer_step: SSD needs d_count");
-    optimizer_step_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(static_cast<OptState *>(d_state), d_metric, d_count,
-                                                              metric_is_ssd, d_A);
+    optimizer_step_kernel<unsigned long long><<<1, 32, 0, (cudaStream_t)stream>>>(static_cast<OptState *>(d_state), d_metric,
+                                                                                  d_count, metric_is_ssd, d_A);
+    CUDA_TRY(cudaGetLastError());
+    return MIA_OK;
+}
+
+int mia_metric_pack(const double *d_metric, const unsigned long long *d_count, int n_local, int q0, int n_total,
+                    double *d_packed, void *stream)
+{
+    if (!d_packed || (n_local > 0 && !d_metric)) return fail(MIA_ERR_ARG, "mia_metric_pack: null pointer");
+    if (n_total < 1 || n_total > MIA_MAX_MATS || n_local < 0 || q0 < 0 || q0 + n_local > n_total)
+        return fail(MIA_ERR_ARG, "mia_metric_pack: need 0 <= q0, q0 + n_local <= n_total <= %d", MIA_MAX_MATS);
+    metric_pack_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(d_metric, d_count, n_local, q0, n_total, d_packed);
+    CUDA_TRY(cudaGetLastError());
+    return MIA_OK;
+}
+
+int mia_optimizer_step_packed(void *d_state, const double *d_packed, int metric_is_ssd, double *d_A, double *d_A_slab,
+                              int k0, void *stream)
+{
+    if (!d_state || !d_packed || !d_A) return fail(MIA_ERR_ARG, "mia_optimizer_step_packed: null pointer");
+    optimizer_step_kernel<double><<<1, 32, 0, (cudaStream_t)stream>>>(static_cast<OptState *>(d_state), d_packed,
+                                                                      d_packed + kOptProbes, metric_is_ssd, d_A, d_A_slab, k0);
     CUDA_TRY(cudaGetLastError());
     return MIA_OK;
 }

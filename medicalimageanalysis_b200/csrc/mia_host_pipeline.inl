@@ -14,7 +14,7 @@ struct HostCtx {
 
 constexpr int kMaxDevices = 16;
 HostCtx g_host[kMaxDevices];
-std::mutex g_host_mu;
+std::mutex g_host_mu[kMaxDevices];       // one pipeline per device; calls on different devices do not serialise
 
 int ensure_events(std::vector<cudaEvent_t> &v, size_t n)
 {
@@ -46,7 +46,7 @@ extern "C" {
 void *mia_host_alloc(size_t bytes)
 {
     void *p = nullptr;
-    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) {
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) {
         fail(MIA_ERR_CUDA, "mia_host_alloc: cudaHostAlloc(%zu) failed", bytes);
         return nullptr;
     }
@@ -59,6 +59,19 @@ int mia_host_free(void *p)
     return MIA_OK;
 }
 
+int mia_host_register(void *p, size_t bytes)
+{
+    if (!p || !bytes) return fail(MIA_ERR_ARG, "mia_host_register: null pointer or empty range");
+    CUDA_TRY(cudaHostRegister(p, bytes, cudaHostRegisterPortable));
+    return MIA_OK;
+}
+
+int mia_host_unregister(void *p)
+{
+    if (p) CUDA_TRY(cudaHostUnregister(p));
+    return MIA_OK;
+}
+
 int mia_resample_rigid_host(const void *h_mov, int mov_dtype, const int mdims[3], void *h_out,
                             int out_dtype, const int odims[3], const double A[12], double background,
                             int mode, int device)
@@ -67,7 +80,7 @@ int mia_resample_rigid_host(const void *h_mov, int mov_dtype, const int mdims[3]
     if (!dims_ok(mdims) || !dims_ok(odims)) return fail(MIA_ERR_ARG, "mia_resample_rigid_host: dims must be positive");
     if (!dtype_ok(mov_dtype) || !dtype_ok(out_dtype)) return fail(MIA_ERR_DTYPE, "mia_resample_rigid_host: bad dtype");
     if (device < 0 || device >= kMaxDevices) return fail(MIA_ERR_ARG, "mia_resample_rigid_host: bad device");
-    std::lock_guard<std::mutex> lock(g_host_mu);
+    std::lock_guard<std::mutex> lock(g_host_mu[device]);
     int prev = 0;
     CUDA_TRY(cudaGetDevice(&prev));
     CUDA_TRY(cudaSetDevice(device));
@@ -93,7 +106,10 @@ int mia_resample_rigid_host(const void *h_mov, int mov_dtype, const int mdims[3]
         if (n > (size_t)nz) n = (size_t)nz;
         return (int)n;
     };
-    const int nin = nslabs(mbytes, mdims[2]), nout = nslabs(obytes, odims[2]);
+    // output slabs start on multiples of the kernels' 8-plane tile depth: every slab then runs the very tiles a
+    // one-piece launch runs, and the host path returns the bytes of the device path
+    const int otiles = (odims[2] + 7) / 8;
+    const int nin = nslabs(mbytes, mdims[2]), nout = nslabs(obytes, otiles);
     if (ensure_events(c.ev_in, nin) || ensure_events(c.ev_k, nout)) {
         cudaSetDevice(prev);
         return fail(MIA_ERR_CUDA, "mia_resample_rigid_host: event creation failed");
@@ -108,7 +124,7 @@ int mia_resample_rigid_host(const void *h_mov, int mov_dtype, const int mdims[3]
             rc = fail(MIA_ERR_CUDA, "mia_resample_rigid_host: H2D failed");
     }
     for (int o = 0; o < nout && rc == MIA_OK; ++o) {
-        const int k0 = zsplit(odims[2], nout, o), k1 = zsplit(odims[2], nout, o + 1);
+        const int k0 = 8 * zsplit(otiles, nout, o), k1 = o + 1 == nout ? odims[2] : 8 * zsplit(otiles, nout, o + 1);
         // highest moving z plane this output slab can touch (8 corners, +1 for the upper tap)
         double zmax = -1e300;
         for (int cc = 0; cc < 8; ++cc) {

@@ -78,13 +78,28 @@ __device__ inline void opt_emit_probes(const OptState *st, double *dA)
     }
 }
 
+__device__ inline void opt_shift_probes(const double *dA, double *dA_slab, int k0)
+{
+    for (int q = 0; q < kOptProbes; ++q)
+        for (int r = 0; r < 3; ++r) {
+            const double *a = dA + 12 * q + 4 * r;
+            double *b = dA_slab + 12 * q + 4 * r;
+            b[0] = a[0]; b[1] = a[1]; b[2] = a[2];
+            b[3] = a[3] + a[2] * (double)k0;
+        }
+}
+
 __global__ void optimizer_init_kernel(OptState *st, double *dA)
 {
     if (threadIdx.x == 0 && blockIdx.x == 0) opt_emit_probes(st, dA);
 }
 
-__global__ void optimizer_step_kernel(OptState *st, const double *metric, const unsigned long long *count,
-                                      int metric_is_ssd, double *dA)
+// CNT = unsigned long long (the metric kernels' own counters) or double (the packed, all-reduced buffer of the sharded
+// loops).  dA_slab, when given, receives the same probes shifted to a z-slab that starts at fixed plane k0
+// (A[:, 3] += A[:, 2] * k0): the sharded loop then needs no kernel of its own for the shift.
+template <typename CNT>
+__global__ void optimizer_step_kernel(OptState *st, const double *metric, const CNT *count, int metric_is_ssd, double *dA,
+                                      double *dA_slab = nullptr, int k0 = 0)
 {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     double c[kOptProbes];
@@ -129,6 +144,20 @@ __global__ void optimizer_step_kernel(OptState *st, const double *metric, const 
         }
     }
     opt_emit_probes(st, dA);
+    if (dA_slab) opt_shift_probes(dA, dA_slab, k0);
+}
+
+// packed[0 .. n_total) = metric, packed[n_total .. 2 n_total) = (double)count, both zero outside this rank's share
+// [q0, q0 + n_local): ONE all-reduce(SUM) of 2 * n_total doubles then combines z-slabs (every rank holds all probes,
+// q0 = 0) or probe shares (adding zeros is exact).  Counts stay exact in float64 below 2^53 voxels.
+__global__ void metric_pack_kernel(const double *metric, const unsigned long long *count, int n_local, int q0, int n_total,
+                                   double *packed)
+{
+    const int q = threadIdx.x;
+    if (q >= n_total) return;
+    const bool mine = q >= q0 && q < q0 + n_local;
+    packed[q] = mine ? metric[q - q0] : 0.0;
+    packed[n_total + q] = (mine && count) ? (double)count[q - q0] : 0.0;
 }
 
 }  // namespace mia

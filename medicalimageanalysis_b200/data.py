@@ -8,6 +8,7 @@ class Data(object):
     rigid = {}
     image_list = []
     rigid_list = []
+    deformable_list = []          # names of displacement fields read so far (read/mhd.py:222-233 resolves collisions on it)
 
     @classmethod
     def clear(cls):
@@ -16,6 +17,7 @@ class Data(object):
         cls.rigid = {}
         cls.image_list = []
         cls.rigid_list = []
+        cls.deformable_list = []
 
     @classmethod
     def delete_image(cls, image_name):

@@ -107,6 +107,21 @@ def pinned_empty(shape, dtype):
     return arr
 
 
+def host_register(arr):
+    """Page-lock the memory of a NumPy array the caller owns (``mia_host_register``), e.g. this rank's planes of a shared
+    mapping.  Returns a handle to pass to ``host_unregister``."""
+    lib = _lib.load()
+    arr = np.asarray(arr)
+    if not arr.flags["C_CONTIGUOUS"] or arr.nbytes == 0:
+        raise ValueError("host_register needs a non-empty C-contiguous array")
+    check(lib.mia_host_register(arr.ctypes.data, arr.nbytes))
+    return arr.ctypes.data
+
+
+def host_unregister(handle):
+    check(_lib.load().mia_host_unregister(handle))
+
+
 def permute_axes(vol, perm, flip, out=None):
     """Exact ``np.flip(np.transpose(vol, perm), flipped axes)`` on the device."""
     lib = _lib.load()

@@ -5,8 +5,11 @@ Rank r owns the z-slab ``[k0_r, k1_r)`` of the fixed lattice (boundaries on mult
 8-plane tile so every rank runs whole tiles), evaluates it with the matrix shifted by its first plane,
 ``A[:, 3] += A[:, 2] * k0`` -- the rule ``mia_resample_rigid_host`` uses for its own z-slab pipeline --
 and the partial ``{ssd, count}`` or joint histograms are combined by ``all_reduce(SUM)`` over NCCL / NVLink
-(``gloo`` in the CPU tests).  The moving volume is replicated: ``A`` changes every iteration of a
-registration loop, and even config 5 (2.5 GB) is small next to 180 GB of HBM.
+(``gloo`` in the CPU tests).  In a registration loop the moving volume is replicated: ``A`` changes every iteration,
+and even config 5 (2.5 GB) is small next to 180 GB of HBM.  A one-shot resample (``Rigid.create_image``) needs only the
+moving planes its slab touches: ``resample_slab`` / ``resample_host_slab`` take ``geometry.slab_moving_zrange`` -- the
+bounding box of the slab under ``A`` plus a one-plane halo -- so that N ranks share ONE volume with 1/N of the
+traffic each.
 
 Volumes too small to cut (config 3: 256^3 is 50 us of work per evaluation) shard over the 13 PROBES of an
 optimiser iteration instead: rank r evaluates probes ``[q0_r, q1_r)`` on a replicated pair and the
@@ -101,29 +104,122 @@ def sharded_hist(evaluate_slab, nz, A, bins, rank, world, group=None):
     return h, cnt
 
 
-def resample_slab(moving, A, out_shape, rank, world, background=-3001.0, mode="vtk"):
-    """This rank's z-slab of a resample (no collective).  Returns ``(tensor [k1-k0, y, x], (k0, k1))``."""
-    from . import kernels
+def slab_plan(A, out_shape, mov_nz, rank, world):
+    """This rank's share of a one-shot resample: output planes ``[k0, k1)``, the moving planes ``[z0, z1)`` they
+    touch (``geometry.slab_moving_zrange``: bounding box + one plane of halo, clipped) and the matrix that maps the
+    slab's own index space to the sub-volume's: ``A[:, 3] += A[:, 2] * k0`` and ``A[2, 3] -= z0``.  Because the halo
+    keeps every sample at least one plane away from an artificial face, inside tests and clamps see what they would
+    see in the whole volume: the slab is bit-identical to the same planes of a one-GPU resample."""
+    A = np.asarray(A, dtype=np.float64).reshape(3, 4)
     k0, k1 = slab_of(out_shape[0], rank, world)
     if k1 <= k0:
+        return (k0, k1), (0, 0), A
+    z0, z1 = G.slab_moving_zrange(A, (out_shape[2], out_shape[1], out_shape[0]), k0, k1, mov_nz)
+    As = shift_matrix(A, k0)
+    As[2, 3] -= float(z0)
+    return (k0, k1), (z0, z1), As
+
+
+def resample_slab(moving, A, out_shape, rank, world, background=-3001.0, mode="vtk", moving_z0=0, moving_nz=None):
+    """This rank's z-slab of a resample (no collective).  ``moving`` is a CUDA tensor holding moving planes
+    ``[moving_z0, moving_z0 + len)`` of a volume ``moving_nz`` planes deep -- the whole volume (the defaults), or just
+    what ``slab_plan`` says this rank needs.  Returns ``(tensor [k1-k0, y, x], (k0, k1))``."""
+    from . import kernels
+    nz_total = int(moving_nz) if moving_nz is not None else moving_z0 + moving.shape[0]
+    (k0, k1), (z0, z1), As = slab_plan(A, out_shape, nz_total, rank, world)
+    if k1 <= k0:
         return None, (k0, k1)
-    out = kernels.resample(moving, shift_matrix(np.asarray(A, dtype=np.float64), k0),
-                           (k1 - k0, out_shape[1], out_shape[2]), background=background, mode=mode)
+    if z1 <= z0:                                  # the slab misses the volume altogether: background only
+        z0, z1 = moving_z0, moving_z0 + 1
+        As = shift_matrix(np.asarray(A, dtype=np.float64).reshape(3, 4), k0)
+        As[2, 3] -= float(z0)
+    if z0 < moving_z0 or z1 > moving_z0 + moving.shape[0]:
+        raise ValueError("resident moving planes [%d, %d) do not cover the slab's range [%d, %d)" %
+                         (moving_z0, moving_z0 + moving.shape[0], z0, z1))
+    out = kernels.resample(moving[z0 - moving_z0:z1 - moving_z0], As, (k1 - k0, out_shape[1], out_shape[2]),
+                           background=background, mode=mode)
     return out, (k0, k1)
+
+
+def resample_host_slab(h_moving, A, h_out, rank, world, background=-3001.0, mode="vtk", device=0):
+    """This rank's z-slab of ONE host volume (``Rigid.create_image`` on NumPy arrays, ``structure/rigid.py:646-695``, cut
+    over the GPUs of a box): ``h_moving`` and ``h_out`` are the WHOLE arrays -- typically a shared mapping that every rank
+    opened, pinned with ``kernels.host_register`` -- and only planes ``[z0, z1)`` go up and ``[k0, k1)`` come down,
+    through ``mia_resample_rigid_host`` (H2D / kernel / D2H pipelined).  No collective.  Returns ``(k0, k1), (z0, z1)``."""
+    from . import kernels
+    (k0, k1), (z0, z1), As = slab_plan(A, h_out.shape, h_moving.shape[0], rank, world)
+    if k1 <= k0:
+        return (k0, k1), (z0, z1)
+    if z1 <= z0:
+        h_out[k0:k1] = np.asarray(background).astype(h_out.dtype)
+        return (k0, k1), (z0, z1)
+    kernels.resample_host(h_moving[z0:z1], As, (k1 - k0,) + tuple(h_out.shape[1:]), background=background, mode=mode,
+                          out=h_out[k0:k1], device=device)
+    return (k0, k1), (z0, z1)
+
+
+def _loop_and_read(lib, _lib, torch, dev, cfg, state, one_iteration, center, extra):
+    """Run ``cfg.iterations`` of ``one_iteration`` on the current stream -- ``cfg.graph_iters`` at a time as a replayed
+    CUDA graph when asked (NCCL collectives are capturable; every rank captures the same sequence) -- and read the
+    optimiser state back."""
+    from .registration import N_PROBES, RegistrationResult
+
+    def stream():
+        return ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+    from .registration import _nvtx_wrapped
+    one_iteration = _nvtx_wrapped(torch, one_iteration, "mia.register_rigid_sharded.iteration[%s]" % cfg.metric)
+    done = 0
+    gi = int(cfg.graph_iters)
+    if gi > 0 and cfg.iterations >= gi + 1:
+        one_iteration()                       # warm-up outside capture (lazy module load, NCCL channel set-up)
+        done = 1
+        torch.cuda.synchronize(dev)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            for _ in range(gi):
+                one_iteration()
+        while cfg.iterations - done >= gi:
+            graph.replay()
+            done += gi
+    while done < cfg.iterations:
+        one_iteration()
+        done += 1
+    n = min(cfg.iterations, 4096)
+    params = (ctypes.c_double * 6)()
+    scale = ctypes.c_double()
+    iters, conv, nrej = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    hc = np.zeros(n); hp = np.zeros((n, 6)); hs = np.zeros(n)
+    dp = ctypes.POINTER(ctypes.c_double)
+    _lib.check(lib.mia_optimizer_read(state.data_ptr(), params, ctypes.byref(scale), ctypes.byref(iters),
+                                      ctypes.byref(conv), ctypes.byref(nrej), hc.ctypes.data_as(dp),
+                                      hp.ctypes.data_as(dp), hs.ctypes.data_as(dp), n, stream()))
+    p = np.array(list(params))
+    return RegistrationResult(params=p, matrix=G.params_to_matrix(p, center), iterations=int(iters.value),
+                              converged=bool(conv.value), n_reject=int(nrej.value), cost_history=hc[:iters.value],
+                              param_history=hp[:iters.value], scale_history=hs[:iters.value],
+                              evaluations=N_PROBES * int(iters.value), extra=extra)
 
 
 def register_rigid_sharded(fixed, moving, params0=None, cfg=None, group=None):
     """``registration.register_rigid`` with the fixed lattice cut into z-slabs over the ranks of ``group``.
 
     Every rank passes the same ``fixed`` / ``moving`` images (CUDA arrays on its own device; only this rank's
-    slab of ``fixed.array`` is read).  Per iteration: one fused 13-probe launch on the slab, one
-    ``all_reduce`` of ``{ssd[13], count[13]}`` (208 B) or of the 13 joint histograms (13*B*B*4 B), then the
-    one-thread optimiser kernel -- which sees identical sums on every rank, so all ranks walk the same
-    trajectory without exchanging parameters.  Returns the same ``RegistrationResult`` on every rank."""
+    slab of ``fixed.array`` is read).  Per iteration, all on the device and on one stream:
+
+    * SSD: the fused 13-probe launch on the slab; ``mia_metric_pack`` puts ``{ssd[13], count[13]}`` into ONE float64
+      buffer (counts are exact in float64); ONE ``all_reduce(SUM)`` of 208 bytes; ``mia_optimizer_step_packed``
+      updates the parameters and writes the next probes both globally and shifted to this rank's slab.
+    * MI: the 13 joint histograms of the slab; ONE ``all_reduce(SUM)`` of ``13 * B * B`` uint32 (integer: bit-identical
+      for every world size); MI from the summed histograms; the same device step.
+
+    All ranks see identical sums and walk the same trajectory without exchanging parameters.  With
+    ``cfg.graph_iters > 0`` the loop (collective included) is captured once and replayed.  NVLink traffic per
+    iteration and rank: 208 B (SSD) or 213 KB (MI, 64 bins).  Returns the same ``RegistrationResult`` on every rank."""
     import torch
 
     from . import _lib, kernels
-    from .registration import N_PROBES, RegistrationConfig, RegistrationResult, _intensity_range
+    from .registration import N_PROBES, RegistrationConfig, _intensity_range
     dist = _dist()
     lib = _lib.load()
     cfg = cfg or RegistrationConfig()
@@ -143,8 +239,10 @@ def register_rigid_sharded(fixed, moving, params0=None, cfg=None, group=None):
     ws = kernels.MetricWorkspace(dev, n_mats=N_PROBES, bins=cfg.bins)
     d_A = torch.zeros((N_PROBES, 3, 4), dtype=torch.float64, device=dev)
     d_Aloc = torch.zeros_like(d_A)
+    packed = torch.zeros(2 * N_PROBES, dtype=torch.float64, device=dev)
     state = torch.zeros(int(lib.mia_optimizer_state_bytes()), dtype=torch.uint8, device=dev)
     if not is_ssd:
+        ws.hist.zero_()
         if cfg.frange and cfg.mrange:
             frange, mrange = cfg.frange, cfg.mrange
         else:                                   # ranges must be global: reduce min / max over the slabs
@@ -157,6 +255,7 @@ def register_rigid_sharded(fixed, moving, params0=None, cfg=None, group=None):
                 lo_hi = torch.stack([-neg[0], neg[1]])
             frange = cfg.frange or (float(lo_hi[0]), float(lo_hi[1]))
             mrange = cfg.mrange or _intensity_range(moving.array)
+        hist_i32 = ws.hist.view(torch.int32)    # same bits; counts stay far below 2^31 per bin
 
     def stream():
         return ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
@@ -166,42 +265,30 @@ def register_rigid_sharded(fixed, moving, params0=None, cfg=None, group=None):
                                           _lib.darr(p2w.ravel()), _lib.darr(w2p.ravel()), cfg.rot_step_deg,
                                           cfg.trans_step_mm, cfg.min_step_scale, 0 if is_ssd else 1,
                                           d_A.data_ptr(), stream()))
-        for _ in range(cfg.iterations):
-            if slab is not None:
-                d_Aloc.copy_(d_A)
-                d_Aloc[:, :, 3] += d_A[:, :, 2] * float(k0)
+        d_Aloc.copy_(shift_matrix(d_A, k0))      # once; afterwards the device step keeps it up to date
+
+        def one_iteration():
             if is_ssd:
                 if slab is not None:
                     kernels.resample_ssd(slab, moving.array, d_A=d_Aloc, mode=cfg.mode, ws=ws)
+                    _lib.check(lib.mia_metric_pack(ws.ssd.data_ptr(), ws.count.data_ptr(), N_PROBES, 0, N_PROBES,
+                                                   packed.data_ptr(), stream()))
                 else:
-                    ws.ssd.zero_(); ws.count.zero_()
-                all_reduce_sum(ws.ssd, ws.count, group=group)
-                metric = ws.ssd
+                    _lib.check(lib.mia_metric_pack(None, None, 0, 0, N_PROBES, packed.data_ptr(), stream()))
+                all_reduce_sum(packed, group=group)
             else:
                 if slab is not None:
                     kernels.resample_jointhist(slab, moving.array, frange, mrange, bins=cfg.bins, d_A=d_Aloc,
                                                mode=cfg.mode, ws=ws)
                 else:
-                    ws.hist.zero_(); ws.count.zero_()
-                all_reduce_sum(ws.hist, ws.count, group=group)
+                    ws.hist.zero_()
+                all_reduce_sum(hist_i32, group=group)
                 kernels.mi_from_hist(ws.hist, out=ws.mi)
-                metric = ws.mi
-            _lib.check(lib.mia_optimizer_step(state.data_ptr(), metric.data_ptr(), ws.count.data_ptr(),
-                                              1 if is_ssd else 0, d_A.data_ptr(), stream()))
-        n = min(cfg.iterations, 4096)
-        params = (ctypes.c_double * 6)()
-        scale = ctypes.c_double()
-        iters, conv, nrej = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
-        hc = np.zeros(n); hp = np.zeros((n, 6)); hs = np.zeros(n)
-        dp = ctypes.POINTER(ctypes.c_double)
-        _lib.check(lib.mia_optimizer_read(state.data_ptr(), params, ctypes.byref(scale), ctypes.byref(iters),
-                                          ctypes.byref(conv), ctypes.byref(nrej), hc.ctypes.data_as(dp),
-                                          hp.ctypes.data_as(dp), hs.ctypes.data_as(dp), n, stream()))
-    p = np.array(list(params))
-    return RegistrationResult(params=p, matrix=G.params_to_matrix(p, center), iterations=int(iters.value),
-                              converged=bool(conv.value), n_reject=int(nrej.value), cost_history=hc[:iters.value],
-                              param_history=hp[:iters.value], scale_history=hs[:iters.value],
-                              evaluations=N_PROBES * int(iters.value), extra={"slab": (k0, k1), "world": world})
+                _lib.check(lib.mia_metric_pack(ws.mi.data_ptr(), None, N_PROBES, 0, N_PROBES, packed.data_ptr(), stream()))
+            _lib.check(lib.mia_optimizer_step_packed(state.data_ptr(), packed.data_ptr(), 1 if is_ssd else 0,
+                                                     d_A.data_ptr(), d_Aloc.data_ptr(), int(k0), stream()))
+
+        return _loop_and_read(lib, _lib, torch, dev, cfg, state, one_iteration, center, {"slab": (k0, k1), "world": world})
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -235,14 +322,15 @@ def register_rigid_probe_parallel(fixed, moving, params0=None, cfg=None, group=N
     """``registration.register_rigid`` with the 13 probes of every iteration dealt out over the ranks of
     ``group``; fixed and moving are replicated (CUDA arrays on each rank's own device).
 
-    Per iteration: one fused launch over this rank's probes, MI from its own histograms, one ``all_reduce`` of
-    ``{cost[13], count[13]}`` (208 B, zero outside the rank's share), then the one-thread optimiser kernel on
-    every rank -- identical inputs, so all ranks walk the same trajectory.  Returns the same
-    ``RegistrationResult`` everywhere."""
+    Per iteration: one fused launch over this rank's probes, MI from its own histograms, ``mia_metric_pack`` into the
+    rank's share of ONE float64 buffer ``{cost[13], count[13]}`` (zero elsewhere, so the sum is exact), ONE
+    ``all_reduce(SUM)`` of 208 bytes, then the one-thread optimiser kernel on every rank -- identical inputs, so all
+    ranks walk the same trajectory.  ``cfg.graph_iters > 0`` captures the loop, collective included, in a CUDA graph.
+    Returns the same ``RegistrationResult`` everywhere."""
     import torch
 
     from . import _lib, kernels
-    from .registration import N_PROBES, RegistrationConfig, RegistrationResult, _intensity_range
+    from .registration import N_PROBES, RegistrationConfig, _intensity_range
     dist = _dist()
     lib = _lib.load()
     cfg = cfg or RegistrationConfig()
@@ -262,12 +350,12 @@ def register_rigid_probe_parallel(fixed, moving, params0=None, cfg=None, group=N
     nloc = q1 - q0
     ws = kernels.MetricWorkspace(dev, n_mats=max(nloc, 1), bins=cfg.bins)
     d_A = torch.zeros((N_PROBES, 3, 4), dtype=torch.float64, device=dev)
-    cost = torch.zeros(N_PROBES, dtype=torch.float64, device=dev)
-    count = torch.zeros(N_PROBES, dtype=torch.int64, device=dev)
+    packed = torch.zeros(2 * N_PROBES, dtype=torch.float64, device=dev)
     state = torch.zeros(int(lib.mia_optimizer_state_bytes()), dtype=torch.uint8, device=dev)
     if not is_ssd:
         frange = cfg.frange or _intensity_range(fixed.array)
         mrange = cfg.mrange or _intensity_range(moving.array)
+        ws.mi                                     # allocate outside any graph capture
 
     def stream():
         return ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
@@ -277,32 +365,21 @@ def register_rigid_probe_parallel(fixed, moving, params0=None, cfg=None, group=N
                                           _lib.darr(p2w.ravel()), _lib.darr(w2p.ravel()), cfg.rot_step_deg,
                                           cfg.trans_step_mm, cfg.min_step_scale, 0 if is_ssd else 1,
                                           d_A.data_ptr(), stream()))
-        for _ in range(cfg.iterations):
-            cost.zero_(); count.zero_()
+        mine = d_A[q0:q1]
+
+        def one_iteration():
             if nloc > 0:
-                mine = d_A[q0:q1]
                 if is_ssd:
                     v, c = kernels.resample_ssd(fixed.array, moving.array, d_A=mine, mode=cfg.mode, ws=ws)
                 else:
                     h, c = kernels.resample_jointhist(fixed.array, moving.array, frange, mrange, bins=cfg.bins,
                                                       d_A=mine, mode=cfg.mode, ws=ws)
                     v = kernels.mi_from_hist(h, out=ws.mi[:nloc])
-                cost[q0:q1] = v
-                count[q0:q1] = c
-            all_reduce_sum(cost, count, group=group)
-            _lib.check(lib.mia_optimizer_step(state.data_ptr(), cost.data_ptr(), count.data_ptr(),
-                                              1 if is_ssd else 0, d_A.data_ptr(), stream()))
-        n = min(cfg.iterations, 4096)
-        params = (ctypes.c_double * 6)()
-        scale = ctypes.c_double()
-        iters, conv, nrej = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
-        hc = np.zeros(n); hp = np.zeros((n, 6)); hs = np.zeros(n)
-        dp = ctypes.POINTER(ctypes.c_double)
-        _lib.check(lib.mia_optimizer_read(state.data_ptr(), params, ctypes.byref(scale), ctypes.byref(iters),
-                                          ctypes.byref(conv), ctypes.byref(nrej), hc.ctypes.data_as(dp),
-                                          hp.ctypes.data_as(dp), hs.ctypes.data_as(dp), n, stream()))
-    p = np.array(list(params))
-    return RegistrationResult(params=p, matrix=G.params_to_matrix(p, center), iterations=int(iters.value),
-                              converged=bool(conv.value), n_reject=int(nrej.value), cost_history=hc[:iters.value],
-                              param_history=hp[:iters.value], scale_history=hs[:iters.value],
-                              evaluations=N_PROBES * int(iters.value), extra={"probes": (q0, q1), "world": world})
+                _lib.check(lib.mia_metric_pack(v.data_ptr(), c.data_ptr(), nloc, q0, N_PROBES, packed.data_ptr(), stream()))
+            else:
+                _lib.check(lib.mia_metric_pack(None, None, 0, 0, N_PROBES, packed.data_ptr(), stream()))
+            all_reduce_sum(packed, group=group)
+            _lib.check(lib.mia_optimizer_step_packed(state.data_ptr(), packed.data_ptr(), 1 if is_ssd else 0,
+                                                     d_A.data_ptr(), None, 0, stream()))
+
+        return _loop_and_read(lib, _lib, torch, dev, cfg, state, one_iteration, center, {"probes": (q0, q1), "world": world})

@@ -137,6 +137,18 @@ class DvfRecord(object):
         self.reference_name, self.moving_name = reference_name, moving_name
 
 
+def narrow_for_image(array):
+    """``Image.array`` on this path is int16 or float32.  Other floating types become float32; other integer types
+    become int16 only when every value fits (MET_UCHAR, small MET_USHORT / MET_INT data) and float32 otherwise -- the
+    reference keeps the source dtype (read/mhd.py:185), so a silent wrap of values above 32767 would change the image."""
+    if array.dtype in (torch.int16, torch.float32):
+        return array
+    if array.dtype.is_floating_point:
+        return array.to(torch.float32)
+    lo, hi = int(array.min()), int(array.max())
+    return array.to(torch.int16) if (-32768 <= lo and hi <= 32767) else array.to(torch.float32)
+
+
 class MhdReader(object):
     """``read/mhd.py:60-196`` with the same arguments; ``load()`` registers the image in ``Data`` (or returns a
     ``DvfRecord`` when ``reference_name``, ``moving_name`` and ``dvf`` are given)."""
@@ -171,9 +183,7 @@ class MhdReader(object):
             idx = len(Data.image_list)
             image_name = "%s %02d" % (self.modality, idx + 1) if idx < 9 else "%s %d" % (self.modality, idx + 1)
         dimensions = np.flip(np.asarray(self.mhd["dims"]))
-        array = self.array
-        if array.dtype not in (torch.int16, torch.float32):                 # Image holds int16 or float32
-            array = array.to(torch.float32 if array.dtype.is_floating_point else torch.int16)
+        array = narrow_for_image(self.array)
         creator = CreateImageFromMask(array, np.asarray(self.mhd["origin"]), np.asarray(self.mhd["spacing"]), image_name,
                                       dimensions=dimensions, orientation=np.asarray(self.mhd["direction"]), plane='Axial',
                                       description='Mhd to Image', modality=self.modality, device=self.device)
@@ -181,9 +191,16 @@ class MhdReader(object):
 
     def create_dvf(self):
         """``read/mhd.py:198-252`` (the field and its lattice; no ``Deformable`` registry here)."""
-        name = "%s_%s" % (self.reference_name, self.moving_name)
         if self.array.dim() != 4 or self.array.shape[3] != 3:
             raise ValueError("%s is not a 3-channel displacement field" % self.file)
+        # the reference's name, "DVF_<reference>_<moving>", with the first free "_<n>" suffix on a collision
+        # (read/mhd.py:222-233); the record is entered in Data.deformable_list so that the next one sees it
+        base = "DVF_%s_%s" % (self.reference_name, self.moving_name)
+        name, n = base, 0
+        while name in Data.deformable_list:
+            n += 1
+            name = "%s_%d" % (base, n)
+        Data.deformable_list += [name]
         return DvfRecord(self.array.to(torch.float32), np.asarray(self.mhd["origin"]), np.asarray(self.mhd["spacing"]),
                          np.flip(np.asarray(self.mhd["dims"])), np.asarray(self.mhd["direction"]).reshape(3, 3), name,
                          self.reference_name, self.moving_name)

@@ -55,6 +55,26 @@ class RegistrationResult:
     evaluations: int = 0
     extra: dict = field(default_factory=dict)
 
+    def save(self, path):
+        """Persist the optimiser state as a small ``.npz`` (checkpoint / resume): parameters, step scale,
+        iteration count and the per-iteration history.  ``resume_from`` turns it back into a start point."""
+        scale = float(self.scale_history[-1]) if len(self.scale_history) else 1.0
+        np.savez(path, params=self.params, scale=scale, iterations=self.iterations, converged=self.converged,
+                 n_reject=self.n_reject, cost_history=self.cost_history, param_history=self.param_history,
+                 scale_history=self.scale_history, evaluations=self.evaluations)
+
+
+def resume_from(path, cfg: RegistrationConfig):
+    """``(params0, cfg')`` that continue a saved run: start at its parameters with the probe / step lengths it had
+    reached (the saved step scale folded into ``rot_step_deg`` / ``trans_step_mm``; ``min_step_scale`` is rescaled so
+    that the absolute stopping length is unchanged)."""
+    import dataclasses
+    z = np.load(path if str(path).endswith(".npz") else str(path) + ".npz")
+    scale = float(z["scale"])
+    cfg2 = dataclasses.replace(cfg, rot_step_deg=cfg.rot_step_deg * scale, trans_step_mm=cfg.trans_step_mm * scale,
+                               min_step_scale=cfg.min_step_scale / scale)
+    return np.asarray(z["params"], dtype=np.float64), cfg2
+
 
 def probe_params(params, scale, deltas):
     """The 13 parameter vectors of one iteration: centre, then +h_i, -h_i for i = 0..5."""
@@ -109,6 +129,18 @@ def host_optimizer(evaluate, params0, cfg: RegistrationConfig):
     return RegistrationResult(params=params, matrix=None, iterations=len(hc), converged=converged,
                               n_reject=n_reject, cost_history=np.array(hc), param_history=np.array(hp),
                               scale_history=np.array(hs), evaluations=N_PROBES * len(hc))
+
+
+def _nvtx_wrapped(torch, fn, name):
+    """NVTX range around one optimiser iteration (13 evaluations + the device step), so that a timeline shows the loop
+    structure; host-side markers only, they cost nothing on the device and are legal during graph capture."""
+    def wrapped():
+        torch.cuda.nvtx.range_push(name)
+        try:
+            fn()
+        finally:
+            torch.cuda.nvtx.range_pop()
+    return wrapped
 
 
 def _intensity_range(t):
@@ -181,6 +213,7 @@ def register_rigid(fixed, moving, params0=None, cfg: RegistrationConfig | None =
         if cfg.metric == "mattes":
             ws.hist64                                 # allocate outside any graph capture
             one_iteration = one_iteration_mattes
+        one_iteration = _nvtx_wrapped(torch, one_iteration, "mia.register_rigid.iteration[%s]" % cfg.metric)
         done = 0
         gi = int(cfg.graph_iters)
         if gi > 0 and cfg.iterations >= gi:

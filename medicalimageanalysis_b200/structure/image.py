@@ -26,7 +26,9 @@ class Image(OffAxisMixin):
         array = image.array
         if isinstance(array, np.ndarray):
             if array.dtype not in (np.int16, np.float32):
-                array = array.astype(np.float32 if array.dtype.kind == "f" else np.int16)
+                # other integer types keep their values: int16 when they fit, float32 otherwise (never a silent wrap)
+                fits = array.dtype.kind != "f" and array.size and -32768 <= array.min() and array.max() <= 32767
+                array = array.astype(np.int16 if fits else np.float32)
             array = torch.from_numpy(np.ascontiguousarray(array)).to(device)
         self.array = array.contiguous()
         self.image_name = image.image_name

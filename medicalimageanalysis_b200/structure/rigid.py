@@ -9,7 +9,7 @@ Out of scope: ROI mesh transforms, ICP, VTK slice objects, pickle per
 """
 from __future__ import annotations
 
-import copy
+import itertools
 
 import numpy as np
 
@@ -18,6 +18,9 @@ from .. import kernels
 from ..data import Data
 
 BACKGROUND = -3001          # structure/rigid.py:692
+
+# slice plane -> (array axis [z, y, x] that the plane fixes, the two physical axes (x=0, y=1, z=2) spanning the plane)
+_PLANES = {'Axial': (0, (0, 1)), 'Coronal': (1, (0, 2)), 'Sagittal': (2, (1, 2))}
 
 
 class ResampledImage(object):
@@ -62,17 +65,12 @@ class Display(object):
         self.compute_scroll_max()
 
     def compute_offset(self):
-        """``structure/rigid.py:89-111``."""
-        if self.rigid.inverse:
-            pos = Data.image[self.rigid.moving_name].origin
-        else:
-            pos = Data.image[self.rigid.reference_name].origin
-        self.offset['Axial'][0] = (self.origin[0] - pos[0]) / self.spacing[0]
-        self.offset['Axial'][1] = (self.origin[1] - pos[1]) / self.spacing[1]
-        self.offset['Coronal'][0] = (self.origin[0] - pos[0]) / self.spacing[0]
-        self.offset['Coronal'][1] = (self.origin[2] - pos[2]) / self.spacing[2]
-        self.offset['Sagittal'][0] = (self.origin[1] - pos[1]) / self.spacing[1]
-        self.offset['Sagittal'][1] = (self.origin[2] - pos[2]) / self.spacing[2]
+        """Where the resliced lattice starts relative to the fixed image, in output voxels, per in-plane axis of each
+        slice plane (semantics of ``structure/rigid.py:89-111``; the fixed image is the moving one when inverted)."""
+        fixed = Data.image[self.rigid.moving_name if self.rigid.inverse else self.rigid.reference_name]
+        shift = (np.asarray(self.origin, dtype=float) - np.asarray(fixed.origin, dtype=float)) / np.asarray(self.spacing, dtype=float)
+        for plane, (_, (u, v)) in _PLANES.items():
+            self.offset[plane] = [shift[u], shift[v]]
 
     def compute_scroll_max(self):
         """``structure/rigid.py:237-252``."""
@@ -86,20 +84,14 @@ class Display(object):
         self.slice_location = np.flip(np.round((np.asarray(position) - self.origin) / self.spacing).astype(np.int32))
 
     def compute_array_slice(self, slice_plane):
-        """``structure/rigid.py:60-87``: one 2-D float64 slice (device -> host copy of that slice only)."""
-        array_slice = None
-        if slice_plane == 'Axial':
-            if 0 <= self.slice_location[0] < self.array.shape[0]:
-                array_slice = self.array[int(self.slice_location[0]), :, :]
-        elif slice_plane == 'Coronal':
-            if 0 <= self.slice_location[1] < self.array.shape[1]:
-                array_slice = self.array[:, int(self.slice_location[1]), :]
-        else:
-            if 0 <= self.slice_location[2] < self.array.shape[2]:
-                array_slice = self.array[:, :, int(self.slice_location[2])]
-        if array_slice is None:
+        """One 2-D float64 slice through ``slice_location`` (semantics of ``structure/rigid.py:60-87``; anything that
+        is not Axial / Coronal counts as Sagittal, a location outside the array gives None).  Only that slice crosses
+        PCIe."""
+        axis = _PLANES.get(slice_plane, _PLANES['Sagittal'])[0]
+        index = int(self.slice_location[axis])
+        if not 0 <= index < self.array.shape[axis]:
             return None
-        return array_slice.cpu().numpy().astype(np.double)
+        return self.array.select(axis, index).cpu().numpy().astype(np.double)
 
     def compute_matrix_pixel_to_position(self):
         """``structure/rigid.py:113-120``."""
@@ -130,20 +122,15 @@ class Rigid(object):
         self.display = Display(self)
 
     def add_rigid(self, rigid_name):
-        """``structure/rigid.py:434-466``."""
+        """Register this object in ``Data.rigid`` (semantics of ``structure/rigid.py:434-466``): an unnamed rigid is
+        called ``<reference>_<moving>`` (``..._combo`` when a combo matrix is set) and takes the first free ``_<n>``
+        suffix, n = 1, 2, ..., if that name exists."""
         if rigid_name is None:
-            if np.array_equal(self.combo_matrix, np.identity(4)):
-                rigid_name = self.reference_name + '_' + self.moving_name
-            else:
-                rigid_name = self.reference_name + '_' + self.moving_name + '_combo'
-            if rigid_name in Data.rigid_list:
-                n = 0
-                while True:
-                    n += 1
-                    new_name = copy.deepcopy(rigid_name + '_' + str(n))
-                    if new_name not in Data.rigid_list:
-                        rigid_name = new_name
-                        break
+            base = '%s_%s' % (self.reference_name, self.moving_name)
+            if not np.array_equal(self.combo_matrix, np.identity(4)):
+                base += '_combo'
+            candidates = itertools.chain([base], ('%s_%d' % (base, n) for n in itertools.count(1)))
+            rigid_name = next(name for name in candidates if name not in Data.rigid_list)
         Data.rigid[rigid_name] = self
         Data.rigid_list += [rigid_name]
         return rigid_name
@@ -193,27 +180,22 @@ class Rigid(object):
         offset = np.dot(fixed_center - np.asarray(location, dtype=float), normal_hat)
         return fixed_center - offset * normal_hat
 
+    def _apply_increment(self, transform):
+        """Compose an increment given in the FIXED image's frame into ``matrix`` and refresh the display: the inverted
+        rigid takes it on the left, the forward one takes its inverse on the right (``structure/rigid.py:966-970, 981-985``)."""
+        self.matrix = transform @ self.matrix if self.inverse else self.matrix @ np.linalg.inv(transform)
+        self.display.compute_reslice()
+
     def update_rotation(self, center=None, r_x=0, r_y=0, r_z=0, slice_plane=None, location=None):
-        """``structure/rigid.py:950-974``."""
+        """Rotate by 'xyz' Euler degrees about ``center`` (default: the fixed image centre, optionally projected on a
+        slice plane) -- ``structure/rigid.py:950-974``."""
         if center is None:
             center = self.retrieve_center(slice_plane=slice_plane, location=location)
-        transform = G.pivot_transform(center, r_x, r_y, r_z)
-        if self.inverse:
-            self.matrix = transform @ self.matrix
-        else:
-            self.matrix = self.matrix @ np.linalg.inv(transform)
-        self.display.compute_reslice()
-        self.display.compute_scroll_max()
+        self._apply_increment(G.pivot_transform(center, r_x, r_y, r_z))
 
     def update_translation(self, t_x=0, t_y=0, t_z=0):
-        """``structure/rigid.py:976-989``."""
-        T = G.translation_transform(t_x, t_y, t_z)
-        if self.inverse:
-            self.matrix = T @ self.matrix
-        else:
-            self.matrix = self.matrix @ np.linalg.inv(T)
-        self.display.compute_reslice()
-        self.display.compute_scroll_max()
+        """Translate by millimetres -- ``structure/rigid.py:976-989``."""
+        self._apply_increment(G.translation_transform(t_x, t_y, t_z))
 
     def pre_alignment(self, superior=False, center=False, origin=False):
         """``structure/rigid.py:718-740``."""
@@ -233,10 +215,10 @@ class Rigid(object):
         return self.matrix[:3, 3]
 
     def retrieve_array_plane(self, slice_plane, solo=None, position=None):
-        """``structure/rigid.py:759-784``."""
+        """The slice of the resliced volume a viewer shows (``structure/rigid.py:759-784``): resample on first use; unless
+        the caller scrolls on its own (``solo``), move the slice location to ``position`` first."""
         if self.display.array is None:
             self.display.compute_reslice()
-            self.display.compute_scroll_max()
         if solo is None:
             self.display.compute_slice_location(position=position)
         return self.display.compute_array_slice(slice_plane=slice_plane)

@@ -52,8 +52,23 @@ def test_dvf_mhd_four_dimensional_payload(cuda_device, tmp_path):
     f = np.random.default_rng(2).standard_normal((6, 8, 10, 3)).astype(np.float32)
     write_mhd(str(tmp_path / "dvf.mhd"), torch.from_numpy(f).to(cuda_device), spacing=(2.0, 2.0, 2.0))
     rec = MhdReader(str(tmp_path / "dvf.mhd"), reference_name="CT 01", moving_name="CT 02", dvf=True).load()
-    assert rec.registration_name == "CT 01_CT 02"
+    assert rec.registration_name == "DVF_CT 01_CT 02"                        # the reference's name, read/mhd.py:222-224
     assert np.array_equal(rec.dvf.cpu().numpy(), f) and list(rec.dimensions) == [6, 8, 10]
+    again = MhdReader(str(tmp_path / "dvf.mhd"), reference_name="CT 01", moving_name="CT 02", dvf=True).load()
+    assert again.registration_name == "DVF_CT 01_CT 02_1"                    # collision suffix, read/mhd.py:226-233
+
+
+def test_unsigned_short_volume_is_not_wrapped(cuda_device, tmp_path):
+    """MET_USHORT data above 32767 must keep its values (the reference keeps the source dtype): it becomes float32, and
+    data that fits int16 stays int16."""
+    from medicalimageanalysis_b200.structure.image import Image
+    from types import SimpleNamespace
+    big = (np.arange(4 * 5 * 8, dtype=np.uint16).reshape(4, 5, 8) * 400)          # up to 63600
+    small = (np.arange(4 * 5 * 8, dtype=np.uint16).reshape(4, 5, 8) * 3)
+    for arr, want in ((big, torch.float32), (small, torch.int16)):
+        src = SimpleNamespace(array=arr, image_name="u16", spacing=(1, 1, 1), origin=(0, 0, 0), image_matrix=np.identity(3))
+        img = Image(src, device=cuda_device)
+        assert img.array.dtype == want and np.array_equal(img.array.cpu().numpy().astype(np.int64), arr.astype(np.int64))
 
 
 @pytest.mark.parametrize("dtype", [np.int16, np.float32])

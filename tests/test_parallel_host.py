@@ -164,3 +164,75 @@ def test_gloo_probe_parallel_walks_the_single_process_trajectory(world):
     for _, params, hist in got:                      # every rank, bit for bit (adding zeros is exact)
         assert np.array_equal(params, want.params) and np.array_equal(hist, want.cost_history)
     assert want.cost_history[-1] < want.cost_history[0]
+
+
+# ---------------------------------------------------------------------------------------------------------
+# one-shot resample cut into z-slabs, each rank holding only the moving planes its slab touches (halo)
+
+def _halo_case():
+    shape, sp = (41, 28, 40), (0.9765625, 0.9765625, 2.5)
+    g = G.Grid((shape[2], shape[1], shape[0]), sp, tuple(-0.5 * np.array(sp) * np.array(shape[::-1])))
+    mov = make_phantom(shape, "CT", seed=6, spacing=sp)
+    M = G.params_to_matrix([3, -2, 4, 5, -3, 7], (0, 0, 0))
+    origin, dims = G.autocrop_extent(g, M, sp, convention="vtk")
+    A = G.compose_index_matrix(G.Grid(dims, sp, origin), g, M, convention="vtk")
+    return mov, A, dims
+
+
+@pytest.mark.parametrize("mode", ["vtk", "itk"])
+def test_slab_plan_halo_reproduces_the_whole_volume(mode):
+    """Resampling slab by slab from the halo sub-volume only gives the bytes of the one-piece resample, for any
+    number of ranks (empty trailing slabs included)."""
+    mov, A, dims = _halo_case()
+    oshape = (dims[2], dims[1], dims[0])
+    whole = native.reslice(mov, A, dims, -3001.0, mode)
+    for world in (1, 2, 3, 5, 8):
+        out = np.full(oshape, 7, dtype=np.int16)
+        touched = 0
+        for rank in range(world):
+            (k0, k1), (z0, z1), As = P.slab_plan(A, oshape, mov.shape[0], rank, world)
+            if k1 <= k0:
+                continue
+            assert 0 <= z0 < z1 <= mov.shape[0]
+            touched += z1 - z0
+            out[k0:k1] = native.reslice(mov[z0:z1], As, (dims[0], dims[1], k1 - k0), -3001.0, mode)
+        assert np.array_equal(out, whole), world
+        if world >= 5:
+            assert touched < 0.6 * world * mov.shape[0]          # each rank holds a fraction of the volume, not all of it
+
+
+def _halo_worker(rank, world, port, path_in, path_out, shape_in, shape_out, A):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        h_in = np.memmap(path_in, dtype=np.int16, mode="r", shape=shape_in)       # ONE host volume, shared by the ranks
+        h_out = np.memmap(path_out, dtype=np.int16, mode="r+", shape=shape_out)
+        (k0, k1), (z0, z1), As = P.slab_plan(A, shape_out, shape_in[0], rank, world)
+        if k1 > k0:
+            h_out[k0:k1] = native.reslice(np.ascontiguousarray(h_in[z0:z1]), As, (shape_out[2], shape_out[1], k1 - k0),
+                                          -3001.0, "vtk")
+            h_out.flush()
+        planes = torch.tensor([z1 - z0], dtype=torch.int64)
+        dist.all_reduce(planes)                                                   # doubles as the completion barrier
+        assert int(planes[0]) < world * shape_in[0]
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gloo_two_ranks_fill_one_shared_output_from_their_halos(tmp_path):
+    mov, A, dims = _halo_case()
+    oshape = (dims[2], dims[1], dims[0])
+    path_in, path_out = str(tmp_path / "in.raw"), str(tmp_path / "out.raw")
+    mov.tofile(path_in)
+    np.full(oshape, 7, dtype=np.int16).tofile(path_out)
+    ctx = mp.get_context("spawn")
+    port = _free_port()
+    procs = [ctx.Process(target=_halo_worker, args=(r, 2, port, path_in, path_out, mov.shape, oshape, A)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    got = np.fromfile(path_out, dtype=np.int16).reshape(oshape)
+    assert np.array_equal(got, native.reslice(mov, A, dims, -3001.0, "vtk"))

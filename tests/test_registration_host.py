@@ -54,3 +54,25 @@ def test_host_optimizer_stays_at_the_optimum():
     res = host_optimizer(oracle_evaluate(g, center, fixed, fixed), np.zeros(6), cfg)
     assert res.cost_history[0] == 0.0
     assert np.allclose(res.params, 0.0, atol=0.6)
+
+
+def test_result_checkpoint_round_trip_and_resume(tmp_path):
+    """the optimiser state persists as a small .npz; a resumed run starts at the saved parameters with the
+    step lengths the first run had reached."""
+    import numpy as np
+    from medicalimageanalysis_b200.registration import RegistrationConfig, host_optimizer, resume_from
+
+    def evaluate(probes):                          # a convex bowl with its minimum at (1, -2, 0.5, 3, 0, -1)
+        t = np.array([1.0, -2.0, 0.5, 3.0, 0.0, -1.0])
+        return [float(np.sum((np.asarray(p) - t) ** 2)) for p in probes]
+    cfg = RegistrationConfig(iterations=25)
+    first = host_optimizer(evaluate, np.zeros(6), cfg)
+    first.save(tmp_path / "state")
+    p0, cfg2 = resume_from(tmp_path / "state", cfg)
+    assert np.array_equal(p0, first.params)
+    s = float(first.scale_history[-1])
+    assert cfg2.rot_step_deg == cfg.rot_step_deg * s and cfg2.min_step_scale * s == cfg.min_step_scale
+    second = host_optimizer(evaluate, p0, cfg2)
+    assert second.cost_history[-1] <= first.cost_history[-1]
+    z = np.load(str(tmp_path / "state") + ".npz")
+    assert int(z["iterations"]) == 25 and z["param_history"].shape == (25, 6)
