@@ -17,6 +17,7 @@
 #include "mia_tile.cuh"
 #include "mia_tile_multi.cuh"
 #include "mia_tile_x2.cuh"
+#include "mia_tile_multi_x2.cuh"
 #include "mia_dvf.cuh"
 #include "mia_dose.cuh"
 #include "mia_pyramid.cuh"
@@ -365,7 +366,7 @@ template <> struct MultiCfg<int16_t> : MultiCfgT<MIA_MULTI_I16> {};
 template <> struct MultiCfg<float> : MultiCfgT<MIA_MULTI_F32> {};
 
 template <typename TM, bool VTK, bool MASK = false>
-int launch_multi(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream_t s)
+int launch_multi(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream_t s, FitGate gate = FitGate{0, 0, 0, 0, 0, 0, 0, 0})
 {
     using BOX = typename MultiBox<TM>::BOX;
     constexpr int NST = MultiCfg<TM>::NST, G = MultiCfg<TM>::G;
@@ -392,7 +393,7 @@ int launch_multi(const CUtensorMap &map, const KParams &p, int n_mats, cudaStrea
     long long gx = (long long)sm_count() * nb;
     if (gx > p.ntiles) gx = p.ntiles;
     if (gx > kMaxGridX) gx = kMaxGridX;
-    k<<<dim3((unsigned)gx, 1, 1), threads, smem, s>>>(map, p, n_mats);
+    k<<<dim3((unsigned)gx, 1, 1), threads, smem, s>>>(map, p, n_mats, gate);
     CUDA_TRY(cudaGetLastError());
     g_last_path = 2;
     return MIA_OK;
@@ -406,7 +407,7 @@ bool multi_path_disabled()
 
 template <typename TM>
 int try_multi_t(int mode, const void *d_mov, const int mdims[3], const double *A_host, int n_mats, KParams p,
-                cudaStream_t s, bool &launched)
+                cudaStream_t s, bool &launched, FitGate gate = FitGate{0, 0, 0, 0, 0, 0, 0, 0})
 {
     using BOX = typename MultiBox<TM>::BOX;
     launched = false;
@@ -420,8 +421,76 @@ int try_multi_t(int mode, const void *d_mov, const int mdims[3], const double *A
     if ((long long)p.ox * p.oy * kTZ >= 0x7fffffffLL) return MIA_OK;
     launched = true;
     if (p.fmask)
-        return mode == MIA_MODE_VTK ? launch_multi<TM, true, true>(map, p, n_mats, s) : launch_multi<TM, false, true>(map, p, n_mats, s);
-    return mode == MIA_MODE_VTK ? launch_multi<TM, true>(map, p, n_mats, s) : launch_multi<TM, false>(map, p, n_mats, s);
+        return mode == MIA_MODE_VTK ? launch_multi<TM, true, true>(map, p, n_mats, s, gate) : launch_multi<TM, false, true>(map, p, n_mats, s, gate);
+    return mode == MIA_MODE_VTK ? launch_multi<TM, true>(map, p, n_mats, s, gate) : launch_multi<TM, false>(map, p, n_mats, s, gate);
+}
+
+bool x2_path_disabled();      // MIA_NO_X2 (defined with the one-matrix x-pair kernel below)
+
+// x-pair multi-matrix SSD kernel (mia_tile_multi_x2.cuh): box 128 x 16 x 15 (60 KB), 2 ring stages, 2 consumer groups.
+// The box budget is what the per-thread accumulators (96 KB) leave of one SM's shared memory: BY * BZ <= 246.  16 x 15
+// takes about 5 degrees about z and 4 degrees of tilt on an isotropic lattice, probe spread included; beyond that the
+// 32-wide kernel serves the launch.
+#ifndef MIA_MX2_BY
+#define MIA_MX2_BY 16
+#endif
+#ifndef MIA_MX2_BZ
+#define MIA_MX2_BZ 15
+#endif
+struct MultiX2Cfg {
+    using BOX = Box<128, MIA_MX2_BY, MIA_MX2_BZ>;
+    static constexpr int NST = 2, G = 2;
+};
+
+template <bool VTK>
+int launch_multi_x2(const CUtensorMap &map, const KParams &p, int n_mats, cudaStream_t s, FitGate gate)
+{
+    using BOX = MultiX2Cfg::BOX;
+    constexpr int NST = MultiX2Cfg::NST, G = MultiX2Cfg::G;
+    constexpr int threads = 32 * (kX2Consumers * G + 1);
+    auto k = tile_multi_x2_kernel<VTK, BOX, NST, G>;
+    const size_t smem = MultiX2Smem<BOX, NST, G>::kBytes;
+    static std::mutex mu;
+    static std::map<int, int> occ;                         // device -> resident CTAs per SM
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    int nb = 0;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        auto it = occ.find(dev);
+        if (it == occ.end()) {
+            CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k, threads, smem));
+            if (nb < 1) return fail(MIA_ERR_UNSUPPORTED, "x-pair multi-matrix kernel does not fit on this device (%zu B smem)", smem);
+            occ[dev] = nb;
+        } else {
+            nb = it->second;
+        }
+    }
+    long long gx = (long long)sm_count() * nb;
+    if (gx > p.ntiles) gx = p.ntiles;
+    if (gx > kMaxGridX) gx = kMaxGridX;
+    k<<<dim3((unsigned)gx, 1, 1), threads, smem, s>>>(map, p, n_mats, gate);
+    CUDA_TRY(cudaGetLastError());
+    g_last_path = 6;
+    return MIA_OK;
+}
+
+int try_multi_x2(int mode, const void *d_mov, const int mdims[3], int n_mats, KParams p, cudaStream_t s, bool &launched,
+                 FitGate gate)
+{
+    using BOX = MultiX2Cfg::BOX;
+    launched = false;
+    alignas(64) CUtensorMap map;
+    if (!make_tensor_map<int16_t, BOX>(&map, d_mov, mdims)) return MIA_OK;
+    p.ntx = (p.ox + kXW - 1) / kXW;
+    p.nty = (p.oy + kXH - 1) / kXH;
+    p.ntiles = (long long)p.ntx * p.nty * ((p.oz + kXD - 1) / kXD);
+    p.magic_fold = 0u - kMagicBits * (unsigned)((BOX::kY + 1) * BOX::kX + 1) * 2u;
+    if (p.ntiles > 0x7fffffffLL) return MIA_OK;
+    if ((long long)p.ox * p.oy * kXD >= 0x7fffffffLL) return MIA_OK;
+    launched = true;
+    return mode == MIA_MODE_VTK ? launch_multi_x2<true>(map, p, n_mats, s, gate) : launch_multi_x2<false>(map, p, n_mats, s, gate);
 }
 
 // SSD of 2..kMaxMulti matrices without a stored output; p.dA is set (metric_common stages host matrices).
@@ -431,7 +500,30 @@ int try_multi(int dtype, int mode, const void *d_mov, const int mdims[3], const 
     launched = false;
     if (n_mats < 2 || n_mats > kMaxMulti || !p.dA || tile_path_disabled() || multi_path_disabled()) return MIA_OK;
     if (dtype == MIA_F32) return try_multi_t<float>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
-    return try_multi_t<int16_t>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
+    // int16: the x-pair kernel when every probe fits its box, the 32-wide kernel otherwise.  Host matrices are tested
+    // here; device matrices by the kernels themselves (FitGate: both are enqueued, one returns at once).
+    using XB = MultiX2Cfg::BOX;
+    // Slack 3: measured on a 1024 x 1024 x 304 lattice of 0.5 mm voxels, 13 probes +-0.5 degree / mm: around identity the
+    // x-pair kernel runs 560 Gvoxel/s against 489, around (3, -2, 4) degrees 380 against 405 -- across a 64-wide tile the
+    // probes drift apart twice as far and need several boxes per tile position -- so it takes the launch only while
+    // the centre probe leaves three rows / planes free (about 2 degrees on an isotropic lattice).
+    const FitGate gate_x2{1, kXW - 1, kXH - 1, kXD - 1, XB::kX, XB::kY, XB::kZ, 3};
+    if (x2_path_disabled() || p.fmask) return try_multi_t<int16_t>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
+    if (A_host) {
+        bool fits = true;
+        for (int m = 0; m < n_mats; ++m) fits &= gate_fits(A_host + 12 * m, gate_x2);
+        if (!fits) return try_multi_t<int16_t>(mode, d_mov, mdims, A_host, n_mats, p, s, launched);
+        return try_multi_x2(mode, d_mov, mdims, n_mats, p, s, launched, FitGate{0, 0, 0, 0, 0, 0, 0, 0});
+    }
+    bool l1 = false, l2 = false;
+    int rc = try_multi_x2(mode, d_mov, mdims, n_mats, p, s, l1, gate_x2);
+    if (rc != MIA_OK) return rc;
+    FitGate other = gate_x2;
+    other.mode = l1 ? 2 : 0;
+    rc = try_multi_t<int16_t>(mode, d_mov, mdims, A_host, n_mats, p, s, l2, other);
+    launched = l1 || l2;
+    if (l1) g_last_path = 6;
+    return rc;
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -56,22 +56,20 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t byt
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
 
-// Spin with back-off: a failed probe sleeps `ns` so that waiting warps do not eat issue slots
-// (ncu: the bare try_wait loop was 13 % of all issued instructions).
+// Wait for a phase of an mbarrier.  try_wait blocks in hardware until the phase completes or a time limit passes; the
+// explicit suspend-time hint (nanoseconds) keeps a waiting warp off the issue port for that long.  The first cut looped
+// over nanosleep + try_wait: ncu counted 12 % of all issued instructions in those loops (nanosleep returns after a few
+// nanoseconds on this part), stolen from warps that had work.  NS = hint; the loop only re-arms after a time-out.
 template <int NS>
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
 {
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DONE_%=;\n"
         "WAIT_%=:\n"
-        "nanosleep.u32 %2;\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
         "@!p bra WAIT_%=;\n"
-        "DONE_%=:\n"
-        "}\n" ::"r"(bar), "r"(parity), "n"(NS)
+        "}\n" ::"r"(bar), "r"(parity), "r"((uint32_t)(NS < 1000 ? 20000 : 1000000))
         : "memory");
 }
 
@@ -114,6 +112,42 @@ __device__ __forceinline__ int16_t tile_to_out<int16_t, false>(float v)  // trun
     short r;
     asm("cvt.rzi.sat.s16.f32 %0, %1;" : "=h"(r) : "f"(v));
     return r;
+}
+
+// Device-side kernel selection for matrices that live in device memory (graph-captured registration loops: the host
+// never sees them).  Two kernels that serve the same call are BOTH enqueued with complementary gates; every CTA
+// evaluates the same cheap predicate -- does a tile of (ex+1, ey+1, ez+1) voxels fit a box (bx, by, bz) under every
+// matrix of the launch? -- and the kernel whose gate fails returns at once (a few microseconds), so no round trip
+// through the host is needed and the sequence stays capturable.
+struct FitGate {
+    int mode;              // 0 = off (always run), 1 = run only if every matrix fits, 2 = run only if some matrix does not
+    int ex, ey, ez;        // tile extents minus one
+    int bx, by, bz;        // box
+    int slack;             // rows / planes the fit must leave free (room for the spread of the probes of one iteration)
+};
+
+__host__ __device__ inline bool gate_fits(const double *A, const FitGate &g)
+{
+    const double ext[3] = {(double)g.ex, (double)g.ey, (double)g.ez};
+    const int B[3] = {g.bx, g.by, g.bz};
+    for (int a = 0; a < 3; ++a) {
+        double n = 0.0, q = 0.0;
+        for (int c = 0; c < 3; ++c) {
+            const double d = A[a * 4 + c] * ext[c];
+            if (d < 0.0) n += d; else q += d;
+        }
+        // + 2 taps + 1 for the floor of both ends, + 7 along x for the 16-byte TMA origin (int16)
+        if (!(ceil(q - n) + 3.0 + (a == 0 ? 7.0 : (double)g.slack) <= (double)B[a])) return false;
+    }
+    return true;
+}
+
+__device__ __forceinline__ bool gate_pass(const FitGate &g, const double *dA, int n_mats)
+{
+    if (g.mode == 0) return true;
+    bool all = true;
+    for (int m = 0; m < n_mats; ++m) all &= gate_fits(dA + 12 * m, g);
+    return g.mode == 1 ? all : !all;
 }
 
 // Extent of one output tile in moving index space: negative / positive reach from the tile origin.

@@ -31,6 +31,103 @@ constexpr int kMaxMulti = 16;      // matrices per launch on this path (lane = m
 #endif
 constexpr int kMultiBoxes = MIA_MULTI_BOXES;     // boxes (ring stages) per tile position at most
 
+// Position of a persistent CTA in the tile lattice: tiles are visited as tile = blockIdx.x + n * gridDim.x and
+// (tix, tiy, tiz) advance incrementally.
+struct TileWalk {
+    int tix, tiy, tiz, step_x, step_y, step_z, ntx, nty;
+    __device__ __forceinline__ void advance()
+    {
+        tix += step_x;
+        if (tix >= ntx) { tix -= ntx; ++tiy; }
+        tiy += step_y;
+        if (tiy >= nty) { tiy -= nty; ++tiz; }
+        tiz += step_z;
+    }
+};
+
+// The producer warp of the multi-matrix kernels (this file and mia_tile_multi_x2.cuh): lane m owns matrix m.  Per tile
+// position of TX x TY x TZ voxels it classifies the tile for every matrix, partitions the matrices into up to
+// kMultiBoxes groups that share a box, and feeds one ring stage per group: TileInfo records for all matrices, a header
+// word (1 = last stage of this tile position), one TMA load.
+template <typename TM, class BOX, int NST, int TX, int TY, int TZ>
+__device__ __forceinline__ void multi_producer(const KParams &p, const CUtensorMap *tmap, unsigned char *tsm, unsigned stage_bytes,
+                                               unsigned box_bytes, uint32_t bar0, TileInfo *infos, volatile unsigned *s_hdr,
+                                               const double *s_A, int n_mats, int lane, TileWalk walk, int ntile_mine)
+{
+    constexpr int xalign = 16 / (int)sizeof(TM);
+    const bool have = lane < n_mats;
+    double A[12];
+#pragma unroll
+    for (int q = 0; q < 12; ++q) A[q] = have ? s_A[12 * lane + q] : 0.0;
+    Reach reach;
+    {
+        const double ext[3] = {(double)(TX - 1), (double)(TY - 1), (double)(TZ - 1)};
+        for (int a = 0; a < 3; ++a) {
+            double n = 0.0, q = 0.0;
+            for (int c = 0; c < 3; ++c) {
+                const double d = A[a * 4 + c] * ext[c];
+                if (d < 0.0) n += d; else q += d;
+            }
+            reach.neg[a] = n;
+            reach.pos[a] = q;
+        }
+    }
+    unsigned s = 0, ph = 0;
+    for (int n = 0; n < ntile_mine; ++n) {
+        const TileAabb bb = tile_aabb(A, reach, walk.tix * TX, walk.tiy * TY, walk.tiz * TZ, p.mov.nx, p.mov.ny, p.mov.nz);
+        const bool active = have && !bb.outside;
+        unsigned rem = __ballot_sync(0xffffffffu, active);       // matrices of this tile position still without a box
+        int nbox = 0;
+        do {
+            TileInfo mine;                                       // default: not in this stage (or outside) -> skipped
+            mine.rx = mine.ry = mine.rz = 0;
+            mine.bx = mine.by = mine.bz = 0;
+            mine.cls = kOutside;
+            unsigned boxmask = 0;
+            int ox = 0, oy = 0, oz = 0;
+            if (rem) {
+                const bool inrem = (rem >> lane) & 1u;
+                // candidate origin 1: the corner of the union of the remaining boxes
+                const int big = 0x7fffffff;
+                const int ux = __reduce_min_sync(0xffffffffu, inrem ? bb.lo[0] : big) & ~(xalign - 1);
+                const int uy = __reduce_min_sync(0xffffffffu, inrem ? bb.lo[1] : big);
+                const int uz = __reduce_min_sync(0xffffffffu, inrem ? bb.lo[2] : big);
+                const unsigned fu = __ballot_sync(0xffffffffu, inrem && aabb_fits<BOX>(bb, ux, uy, uz));
+                // candidate origin 2: the first remaining matrix's own box (the centre probe in a registration loop)
+                const int src = __ffs(rem) - 1;
+                const int ax = __shfl_sync(0xffffffffu, bb.lo[0], src) & ~(xalign - 1);
+                const int ay = __shfl_sync(0xffffffffu, bb.lo[1], src);
+                const int az = __shfl_sync(0xffffffffu, bb.lo[2], src);
+                const unsigned fa = __ballot_sync(0xffffffffu, inrem && aabb_fits<BOX>(bb, ax, ay, az));
+                const bool use_union = __popc(fu) >= __popc(fa);
+                ox = use_union ? ux : ax; oy = use_union ? uy : ay; oz = use_union ? uz : az;
+                boxmask = use_union ? fu : fa;
+                // the last box of the position also carries whatever still does not fit (tile_place marks those
+                // kNoFit: per-voxel gather); a matrix whose own tile is larger than the box ends the search
+                const bool last_box = boxmask == 0u || nbox + 1 == kMultiBoxes || (rem & ~boxmask) == 0u;
+                if (inrem && (last_box || ((boxmask >> lane) & 1u))) mine = tile_place<BOX>(bb, ox, oy, oz);
+                rem = last_box ? 0u : (rem & ~boxmask);
+            }
+            if (lane == 0) mbar_wait<1000>(bar0 + 8 * (NST + s), ph ^ 1u);
+            __syncwarp();
+            if (lane < kMaxMulti) infos[s * kMaxMulti + lane] = mine;
+            if (lane == 0) s_hdr[s] = rem == 0u ? 1u : 0u;
+            __syncwarp();
+            if (lane == 0) {
+                if (boxmask) {
+                    mbar_arrive_expect_tx(bar0 + 8 * s, box_bytes);
+                    tma_load_3d(smem_u32(tsm + stage_bytes * s), tmap, bar0 + 8 * s, ox, oy, oz);
+                } else {
+                    mbar_arrive(bar0 + 8 * s);
+                }
+            }
+            if (++s == NST) { s = 0; ph ^= 1u; }
+            ++nbox;
+        } while (rem);
+        walk.advance();
+    }
+}
+
 // One CTA per SM: G groups of 8 consumer warps share every staged box (group g takes matrices g, g+G, ...), one
 // producer warp feeds the ring.  More resident warps than two independent CTAs could hold (their rings would not
 // fit), and the shared-memory budget of a whole SM: a deeper ring plus per-thread accumulators, so that no
@@ -52,8 +149,10 @@ struct MultiSmem {
 
 template <typename TM, typename TF, bool VTK, class BOX, int NST, int G, bool MASK = false>
 __global__ void __launch_bounds__(32 * (kConsumerWarps * G + 1), 1)
-tile_multi_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ KParams p, const int n_mats)
+tile_multi_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ KParams p, const int n_mats,
+                  const FitGate gate)
 {
+    if (!gate_pass(gate, p.dA, n_mats)) return;      // the other kernel of the pair serves this launch (see FitGate)
     using L = MultiSmem<TM, BOX, NST, G>;
     extern __shared__ __align__(1024) unsigned char tsm[];
     __shared__ bool s_last;
@@ -99,67 +198,9 @@ tile_multi_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constan
     };
 
     if (wid == kProducer) {
-        // ---------------- producer warp: lane m owns matrix m ----------------
-        constexpr int xalign = 16 / (int)sizeof(TM);
-        const bool have = lane < n_mats;
-        double A[12];
-#pragma unroll
-        for (int q = 0; q < 12; ++q) A[q] = have ? s_A[12 * lane + q] : 0.0;
-        const Reach reach = tile_reach(A);
-        unsigned s = 0, ph = 0;
-        for (int n = 0; n < ntile_mine; ++n) {
-            const TileAabb bb = tile_aabb(A, reach, tix * kTX, tiy * kTY, tiz * kTZ, p.mov.nx, p.mov.ny, p.mov.nz);
-            const bool active = have && !bb.outside;
-            unsigned rem = __ballot_sync(0xffffffffu, active);       // matrices of this tile position still without a box
-            int nbox = 0;
-            do {
-                TileInfo mine;                                       // default: not in this stage (or outside) -> skipped
-                mine.rx = mine.ry = mine.rz = 0;
-                mine.bx = mine.by = mine.bz = 0;
-                mine.cls = kOutside;
-                unsigned boxmask = 0;
-                int ox = 0, oy = 0, oz = 0;
-                if (rem) {
-                    const bool inrem = (rem >> lane) & 1u;
-                    // candidate origin 1: the corner of the union of the remaining boxes
-                    const int big = 0x7fffffff;
-                    const int ux = __reduce_min_sync(0xffffffffu, inrem ? bb.lo[0] : big) & ~(xalign - 1);
-                    const int uy = __reduce_min_sync(0xffffffffu, inrem ? bb.lo[1] : big);
-                    const int uz = __reduce_min_sync(0xffffffffu, inrem ? bb.lo[2] : big);
-                    const unsigned fu = __ballot_sync(0xffffffffu, inrem && aabb_fits<BOX>(bb, ux, uy, uz));
-                    // candidate origin 2: the first remaining matrix's own box (the centre probe in a registration loop)
-                    const int src = __ffs(rem) - 1;
-                    const int ax = __shfl_sync(0xffffffffu, bb.lo[0], src) & ~(xalign - 1);
-                    const int ay = __shfl_sync(0xffffffffu, bb.lo[1], src);
-                    const int az = __shfl_sync(0xffffffffu, bb.lo[2], src);
-                    const unsigned fa = __ballot_sync(0xffffffffu, inrem && aabb_fits<BOX>(bb, ax, ay, az));
-                    const bool use_union = __popc(fu) >= __popc(fa);
-                    ox = use_union ? ux : ax; oy = use_union ? uy : ay; oz = use_union ? uz : az;
-                    boxmask = use_union ? fu : fa;
-                    // the last box of the position also carries whatever still does not fit (tile_place marks those
-                    // kNoFit: per-voxel gather); a matrix whose own tile is larger than the box ends the search
-                    const bool last_box = boxmask == 0u || nbox + 1 == kMultiBoxes || (rem & ~boxmask) == 0u;
-                    if (inrem && (last_box || ((boxmask >> lane) & 1u))) mine = tile_place<BOX>(bb, ox, oy, oz);
-                    rem = last_box ? 0u : (rem & ~boxmask);
-                }
-                if (lane == 0) mbar_wait<1000>(bar0 + 8 * (NST + s), ph ^ 1u);
-                __syncwarp();
-                if (lane < kMaxMulti) infos[s * kMaxMulti + lane] = mine;
-                if (lane == 0) s_hdr[s] = rem == 0u ? 1u : 0u;
-                __syncwarp();
-                if (lane == 0) {
-                    if (boxmask) {
-                        mbar_arrive_expect_tx(bar0 + 8 * s, L::kBoxBytes);
-                        tma_load_3d(smem_u32(tsm + L::kStageBytes * s), &tmap, bar0 + 8 * s, ox, oy, oz);
-                    } else {
-                        mbar_arrive(bar0 + 8 * s);
-                    }
-                }
-                if (++s == NST) { s = 0; ph ^= 1u; }
-                ++nbox;
-            } while (rem);
-            advance();
-        }
+        TileWalk walk = {tix, tiy, tiz, step_x, step_y, step_z, p.ntx, p.nty};
+        multi_producer<TM, BOX, NST, kTX, kTY, kTZ>(p, &tmap, tsm, L::kStageBytes, L::kBoxBytes, bar0, infos, s_hdr, s_A, n_mats,
+                                                    lane, walk, ntile_mine);
     } else {
         // ---------------- consumers: G groups of 8 warps, every group against the same box ----------------
         // accumulators are private to (group, matrix, thread): the groups drift apart by up to a ring stage and

@@ -124,6 +124,15 @@ __device__ __forceinline__ f32x2 x2_sample(const X2Thread &t, const X2Geom &g, f
     upk_u(tx2, xa, xb); upk_u(ty2, ya, yb); upk_u(tz2, za, zb);
     uint32_t a0 = mad_u32(mad_u32(mad_u32(za, BOX::kY, ya), BOX::kX, xa), 2u, t.ubase);
     uint32_t a1 = mad_u32(mad_u32(mad_u32(zb, BOX::kY, yb), BOX::kX, xb), 2u, t.ubase);
+#ifdef MIA_BOUNDS_CHECK
+    // Debug build (compute-sanitizer is closed on this pool): every tap of both voxels must lie inside the staged box.
+    // t.safe - 4 lane is the stage base.  A violation traps, which surfaces as a launch failure in the caller.
+    {
+        const uint32_t lo = t.safe - 4u * (threadIdx.x & 31u), hi = lo + BOX::kX * BOX::kY * BOX::kZ * 2u;
+        const bool okA = !BORDER || inA, okB = !BORDER || inB;
+        if ((okA && (a0 < lo || a0 + PZ + PY + 4u > hi)) || (okB && (a1 < lo || a1 + PZ + PY + 4u > hi))) __trap();
+    }
+#endif
     if (BORDER) {
         // A voxel outside the volume is stored as background whatever it loads, but its clamped coordinates pile the
         // outside lanes of a warp onto one x with different rows -- one bank, up to 7 wavefronts per LDS with a row

@@ -63,6 +63,39 @@ def main():
     s, c = kernels.resample_ssd(fixed, movs[0], A=A1, mode="itk", ws=ws)
     r.update(path=int(lib.mia_debug_last_path()), ssd=float(s[0]), count=int(c[0]))
     out["c2_ssd_eval_itk"] = r
+    # config 1 (512x512x100): one optimiser iteration = 13 probes in one launch, device matrices (as the loop has them)
+    from medicalimageanalysis_b200.registration import params_to_index_matrix, probe_params
+    shape1 = (100, 512, 512)
+    gq = G.Grid((512, 512, 100), bench.SPACING, tuple(-0.5 * np.array(bench.SPACING) * np.array(shape1[::-1])))
+    f1 = torch.from_numpy(make_phantom(shape1, "CT", seed=1, spacing=bench.SPACING)).to(dev)
+    m1 = torch.from_numpy(make_phantom(shape1, "CT", seed=1, spacing=bench.SPACING, world_matrix=np.linalg.inv(M))).to(dev)
+    p2w, w2p = G.index_to_physical(gq, "itk"), G.physical_to_index(gq, "itk")
+    ws13 = kernels.MetricWorkspace(dev, n_mats=13)
+    for tag, centre in (("identity", np.zeros(6)), ("gt", np.array(bench.GT))):
+        A13 = np.stack([params_to_index_matrix(q, np.zeros(3), p2w, w2p) for q in probe_params(centre, 1.0, np.array([0.5] * 6))])
+        dA = torch.from_numpy(np.ascontiguousarray(A13)).to(dev)
+        r = timeit(lambda: kernels.resample_ssd(f1, m1, d_A=dA, mode="itk", ws=ws13))
+        s, c = kernels.resample_ssd(f1, m1, d_A=dA, mode="itk", ws=ws13)
+        r.update(path=int(lib.mia_debug_last_path()), us_per_eval=r["us_med"] / 13, ssd0=float(s[0]), count0=int(c[0]),
+                 gvoxel_s=13 * f1.numel() / r["us_med"] / 1e3)
+        out["c1_multi13_" + tag] = r
+    # config-5-like slab (1024x1024x304 at 0.5 mm): 13 probes per launch around identity and around the ground truth
+    from medicalimageanalysis_b200.phantom import make_phantom_device
+    del f1, m1, movs, outs, fixed, o
+    torch.cuda.empty_cache()
+    shape5, sp5 = (304, 1024, 1024), (0.5, 0.5, 0.5)
+    g5 = G.Grid((1024, 1024, 304), sp5, (-256.0, -256.0, -76.0))
+    f5 = make_phantom_device(shape5, "CT", seed=5, spacing=sp5, device=dev)
+    m5 = make_phantom_device(shape5, "CT", seed=5, spacing=sp5, world_matrix=np.linalg.inv(M), device=dev)
+    p2w, w2p = G.index_to_physical(g5, "itk"), G.physical_to_index(g5, "itk")
+    for tag, centre in (("identity", np.zeros(6)), ("gt", np.array(bench.GT))):
+        A13 = np.stack([params_to_index_matrix(q, np.zeros(3), p2w, w2p) for q in probe_params(centre, 1.0, np.array([0.5] * 6))])
+        dA = torch.from_numpy(np.ascontiguousarray(A13)).to(dev)
+        r = timeit(lambda: kernels.resample_ssd(f5, m5, d_A=dA, mode="itk", ws=ws13), n=6, warm=2)
+        s, c = kernels.resample_ssd(f5, m5, d_A=dA, mode="itk", ws=ws13)
+        r.update(path=int(lib.mia_debug_last_path()), us_per_eval=r["us_med"] / 13, ssd0=float(s[0]), count0=int(c[0]),
+                 gvoxel_s=13 * f5.numel() / r["us_med"] / 1e3)
+        out["c5slab_multi13_" + tag] = r
     print(json.dumps(out))
 
 

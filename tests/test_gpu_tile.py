@@ -23,6 +23,11 @@ def last_path():
 
 
 MULTI = 2          # mia_tile_multi.cuh
+MULTI_X2 = 6       # mia_tile_multi_x2.cuh: int16, every probe fits the 64-wide tile's box
+
+
+def is_multi(dtype=np.int16):
+    return last_path() in ((MULTI, MULTI_X2) if np.dtype(dtype) == np.int16 else (MULTI,))
 
 
 def grid_of(shape, sp):
@@ -132,7 +137,7 @@ def test_tile_metrics_match_oracle(cuda_device, modality):
     f, m = torch.from_numpy(fixed).to(cuda_device), torch.from_numpy(moving).to(cuda_device)
     ws = kernels.MetricWorkspace(cuda_device, n_mats=13, bins=64)
     s, c = kernels.resample_ssd(f, m, A=A, ws=ws)
-    assert last_path() == MULTI           # 13 unrelated matrices: one shared box, per-tile gather for the misfits
+    assert is_multi(fixed.dtype)           # 13 unrelated matrices: one shared box, per-tile gather for the misfits
     fr = (float(fixed.min()), float(fixed.max()))
     mr = (float(moving.min()), float(moving.max()))
     s, c = s.cpu().numpy().copy(), c.cpu().numpy().copy()
@@ -192,7 +197,7 @@ def test_multi_matrix_ssd_equals_one_matrix_launches(cuda_device, dtype, mode):
                 s, c = kernels.resample_ssd(f, m, d_A=torch.from_numpy(A).to(cuda_device), mode=mode, ws=ws)
             else:
                 s, c = kernels.resample_ssd(f, m, A=A, mode=mode, ws=ws)
-            assert last_path() == MULTI
+            assert is_multi(dtype)
             s, c = s.cpu().numpy().copy(), c.cpu().numpy().copy()
             s2, c2 = kernels.resample_ssd(f, m, A=A, mode=mode, ws=ws)        # workspace reuse: ticket self-reset
             assert np.array_equal(s2.cpu().numpy(), s) and np.array_equal(c2.cpu().numpy(), c)
@@ -203,7 +208,10 @@ def test_multi_matrix_ssd_equals_one_matrix_launches(cuda_device, dtype, mode):
                 # probes half a voxel apart share every box: identical voxel values, summation order only; at 2
                 # voxels / degrees some tiles of some probes miss the shared box and take the per-voxel gather
                 # (float64 row origin: last-bit differences in float32)
-                assert abs(float(s1[0]) - float(s[i])) <= (1e-12 if scale == 1.0 else 1e-7) * float(s1[0])
+                # (int16 launches the x-pair kernel takes: its second voxel of a pair sits at fx + a00 in float32 where
+                # the one-matrix 32-wide kernel has an exact Q31.32 base -- 1e-7 of a voxel, 1e-6 relative in the sum)
+                x2 = np.dtype(dtype) == np.int16
+                assert abs(float(s1[0]) - float(s[i])) <= (1e-6 if x2 else (1e-12 if scale == 1.0 else 1e-7)) * float(s1[0])
             for i in (0, 5, 12):
                 want, n = native.reslice_ssd(fixed, moving, A[i], mode)
                 assert abs(int(c[i]) - n) <= 2 and abs(float(s[i]) - want) <= 1e-5 * want
@@ -223,7 +231,7 @@ def test_multi_matrix_handles_outside_and_ragged(cuda_device):
         prm = [np.concatenate([rng.uniform(-2, 2, 3), rng.uniform(-1, 1, 3) * (40 if i % 3 == 2 else 2)]) for i in range(nm)]
         A = np.stack([G.compose_index_matrix(g, gm, G.params_to_matrix(q, (0, 0, 0))) for q in prm])
         s, c = kernels.resample_ssd(f, m, A=A)
-        assert last_path() == MULTI
+        assert is_multi()
         for i in range(nm):
             want, n = native.reslice_ssd(fixed, mov, A[i], "itk")
             assert abs(int(c[i]) - n) <= 2
@@ -271,7 +279,7 @@ def test_multi_matrix_kernel_groups_probes_into_several_boxes(cuda_device, dtype
                   for p in probe_params(np.array([0.2, -0.1, 0.3, 0.4, -0.2, 0.1]), 1.0, np.array([0.5] * 6))])
     f, m = torch.from_numpy(fixed).to(cuda_device), torch.from_numpy(moving).to(cuda_device)
     s13, c13 = kernels.resample_ssd(f, m, A=A)
-    assert _lib.load().mia_debug_last_path() == 2
+    assert _lib.load().mia_debug_last_path() in (2, 6)
     s13, c13 = s13.clone(), c13.clone()
     for i in range(13):
         s1, c1 = kernels.resample_ssd(f, m, A=A[i])

@@ -119,3 +119,64 @@ def test_rotation_beyond_the_x2_box_takes_the_older_kernels(cuda_device):
     assert last_path() in (1, 4)
     want = reslice.oracle_reslice(mov, A, g.dims, -3001.0, "vtk", np.int16)
     check_parity(got, want, border_band(A, g.dims, g.dims), np.int16, -3001.0)
+
+
+# ---- multi-matrix SSD on the x-pair tile (csrc/mia_tile_multi_x2.cuh) ------------------------------------------------
+MULTI_X2 = 6
+
+
+def _pair(shape, sp, seed):
+    from oracle import native  # noqa: F401  (import check: the oracle is the checker below)
+    g = grid_of(shape, sp)
+    Mgt = G.params_to_matrix([1.0, -0.8, 1.2, 2.0, -1.0, 1.5], (0, 0, 0))
+    fixed = make_phantom(shape, "CT", seed=seed, spacing=sp)
+    moving = make_phantom(shape, "CT", seed=seed, spacing=sp, world_matrix=np.linalg.inv(Mgt))
+    return g, fixed, moving
+
+
+def _probes(g, centre, spread=0.5):
+    from medicalimageanalysis_b200.registration import probe_params
+    p2w, w2p = G.index_to_physical(g), G.physical_to_index(g)
+    return np.ascontiguousarray(np.stack([(w2p @ G.params_to_matrix(q, np.zeros(3)) @ p2w)[:3]
+                                          for q in probe_params(np.asarray(centre, dtype=float), 1.0, np.array([spread] * 6))]))
+
+
+@pytest.mark.parametrize("mode", ["itk", "vtk"])
+@pytest.mark.parametrize("shape", [(40, 56, 136), (21, 45, 200)])          # whole tiles / ragged rows, odd depth
+def test_multi_x2_equals_one_matrix_launches_and_oracle(cuda_device, shape, mode):
+    from oracle import native
+    sp = (1.0, 1.0, 2.0)
+    g, fixed, moving = _pair(shape, sp, seed=21)
+    A = _probes(g, [0.6, -0.5, 0.8, 2.0, -1.0, 1.5])       # within the gate's slack: the x-pair kernel takes the launch
+    f, m = torch.from_numpy(fixed).to(cuda_device), torch.from_numpy(moving).to(cuda_device)
+    for as_device in (False, True):                      # host matrices: fit-tested on the host; device: FitGate
+        kw = {"d_A": torch.from_numpy(A).to(cuda_device)} if as_device else {"A": A}
+        s13, c13 = kernels.resample_ssd(f, m, mode=mode, ws=kernels.MetricWorkspace(cuda_device, n_mats=13), **kw)
+        assert last_path() == MULTI_X2
+        s13, c13 = s13.clone(), c13.clone()
+        for i in range(13):
+            s1, c1 = kernels.resample_ssd(f, m, A=A[i], mode=mode)
+            assert int(c1[0]) == int(c13[i]), i
+            assert abs(float(s1[0]) - float(s13[i])) <= 1e-6 * float(s13[i]), i
+            want, n = native.reslice_ssd(fixed, moving, A[i], mode)
+            assert abs(int(c13[i]) - n) <= 2 and abs(float(s13[i]) - want) <= 1e-5 * want, i
+    s2, c2 = kernels.resample_ssd(f, m, A=A, mode=mode)
+    assert torch.equal(s2, s13) and torch.equal(c2, c13)          # device == host matrices, run to run identical
+
+
+def test_multi_x2_gate_hands_large_rotations_to_the_32_wide_kernel(cuda_device):
+    """Device matrices the host never sees: probes around a 10-degree rotation do not fit the 64-wide tile's box, the
+    x-pair kernel's gate fails and the 32-wide kernel enqueued behind it serves the launch -- same numbers as host
+    matrices (which the host routes to the 32-wide kernel itself) and as the oracle."""
+    from oracle import native
+    shape, sp = (32, 64, 136), (1.0, 1.0, 1.0)
+    g, fixed, moving = _pair(shape, sp, seed=22)
+    A = _probes(g, [0.5, -0.5, 10.0, 1.0, 2.0, -1.0])
+    f, m = torch.from_numpy(fixed).to(cuda_device), torch.from_numpy(moving).to(cuda_device)
+    sh, ch = kernels.resample_ssd(f, m, A=A)
+    assert last_path() != MULTI_X2                        # the host fit test sends these to the older kernels
+    sh, ch = sh.clone(), ch.clone()
+    sd, cd = kernels.resample_ssd(f, m, d_A=torch.from_numpy(A).to(cuda_device), ws=kernels.MetricWorkspace(cuda_device, n_mats=13))
+    assert torch.equal(cd, ch) and float(((sd - sh).abs() / sh).max()) <= 1e-6
+    want, n = native.reslice_ssd(fixed, moving, A[0], "itk")
+    assert abs(int(cd[0]) - n) <= 2 and abs(float(sd[0]) - want) <= 1e-5 * want

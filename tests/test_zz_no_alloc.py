@@ -5,6 +5,7 @@ cudaMalloc).  Called through the C ABI and compared with the existing entry poin
 caller workspace.  This file is named so that pytest collects it last.
 """
 import ctypes
+import gc
 
 import numpy as np
 import pytest
@@ -89,12 +90,13 @@ def test_static_scratch_matches_workspace_entry_point_on_calls_in_a_row(cuda_dev
         results = []
         for A, store in plan:
             n = A.shape[0]
+            gc.collect()                                 # tensors of earlier tests must not be freed in mid-measurement
             torch.cuda.synchronize()
             before = torch.cuda.memory_allocated(cuda_device)
             ssd_s.fill_(-1.0); cnt_s.fill_(-1)
             _lib.check(_call_static(lib, f, m, A, ssd_s, cnt_s, out_s if store else None))
             torch.cuda.synchronize()
-            assert torch.cuda.memory_allocated(cuda_device) == before
+            assert torch.cuda.memory_allocated(cuda_device) <= before          # the call allocates nothing
             ssd_w.fill_(-1.0); cnt_w.fill_(-1)
             _lib.check(_call_workspace(lib, f, m, A, ssd_w, cnt_w, ws, out_w if store else None))
             torch.cuda.synchronize()
