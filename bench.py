@@ -629,6 +629,19 @@ def main():
     for i in range(W):
         step(i)
     path_taken = int(kernels._lib.load().mia_debug_last_path())
+    # One CUDA graph per ring slot: a step is then one graph replay (the same single kernel on the same buffers).  At
+    # N = 8 a slab kernel takes 40 us and the ctypes + tensor-map + launch path of an eager call 56 us: un-graphed, the
+    # timed region would measure the host, not the GPU.
+    torch.cuda.synchronize(dev)
+    graphs = []
+    for i in range(ring):
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            step(i)
+        graphs.append(g)
+
+    def step(i):                                            # noqa: F811  (from here on a step is a graph replay)
+        graphs[i % ring].replay()
     sampler = ClockSampler(local_rank)
     barrier()
     sampler.start()
@@ -687,13 +700,21 @@ def main():
         p_in, p_out = "/dev/shm/mia_bench_%s_in.raw" % tag, "/dev/shm/mia_bench_%s_out.raw" % tag
         pinned = numa_pin(local_rank)
         if rank == 0:
-            mov_h.tofile(p_in)
-            with open(p_out, "wb") as fh:
-                fh.truncate(2 * nvox_out)
+            for pth, nbytes in ((p_in, 2 * mov_h.size), (p_out, 2 * nvox_out)):
+                with open(pth, "wb") as fh:
+                    fh.truncate(nbytes)
         barrier()
         h_in = np.memmap(p_in, dtype=np.int16, mode="r+", shape=SHAPE)
         h_out = np.memmap(p_out, dtype=np.int16, mode="r+", shape=oshape)
-        h_out[k0:k1] = 0                                               # first touch of this rank's output pages
+        # first touch: every rank writes the planes it will read (all ranks hold the same seeded volume, so planes that
+        # two halos share get the same bytes twice) and zeroes the planes it will fill -- the pages then sit on the
+        # NUMA node of the GPU that moves them
+        h_in[z0:z1] = mov_h[z0:z1]
+        h_out[k0:k1] = 0
+        barrier()
+        if rank == 0:
+            h_in[...] = mov_h                                          # planes no halo covers (none here) still get their data
+        barrier()
         handles = [kernels.host_register(h_in[z0:z1]), kernels.host_register(h_out[k0:k1])]
         for _ in range(2):
             parallel.resample_host_slab(h_in, A, h_out, rank, world, device=local_rank)
