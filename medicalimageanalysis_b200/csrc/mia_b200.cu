@@ -304,6 +304,18 @@ template <typename TM> struct TallCfg;
 template <> struct TallCfg<int16_t> : TileCfgT<72, 35, 11, 2, 2, false> {};     // 54 KB per stage; 36-word pitch: a warp that runs down a box column (90 degrees) hits 8 banks, not 1
 template <> struct TallCfg<float> : TileCfgT<48, 36, 11, 2, 1, false> {};       // 76 KB per stage, one CTA per SM
 
+// Third and fourth family: rotations about y (x and z mix: a 32 x 8 x 8 tile turned by 90 degrees spans 8 columns and 32
+// planes) and everything else that is not larger than about 22 voxels along y and z (rotations about x on anisotropic
+// lattices, compound rotations).  The z-heavy box keeps an odd row count so that the plane pitch is 4 (int16) or 28
+// (float32) words mod 32: a warp that runs DOWN the planes (90 degrees about y) then hits 8 banks, not 1 -- the rule
+// the tall family follows for rows.  Any matrix beyond these still takes the per-voxel kernel.
+template <typename TM> struct DeepCfg;
+template <> struct DeepCfg<int16_t> : TileCfgT<56, 13, 36, 2, 2, false> {};     // 51 KB per stage, plane pitch 364 words = 12 mod 32
+template <> struct DeepCfg<float> : TileCfgT<44, 13, 36, 2, 1, false> {};       // 80 KB per stage, plane pitch 572 words = 28 mod 32
+template <typename TM> struct CubeCfg;
+template <> struct CubeCfg<int16_t> : TileCfgT<48, 25, 25, 2, 1, false> {};     // 59 KB per stage
+template <> struct CubeCfg<float> : TileCfgT<40, 25, 25, 2, 1, false> {};       // 98 KB per stage
+
 // One (element type, box) attempt: fit test for host matrices, tensor map, launch.
 template <int METRIC, bool STORE, typename TM, class CFG = TileCfg<TM, METRIC>>
 int try_tile_box(int mode, const void *d_mov, const int mdims[3], const double *A_host, int n_mats, KParams p,
@@ -672,6 +684,18 @@ int mia_resample_rigid(const void *d_mov, int mov_dtype, const int mdims[3], voi
                                   : try_tile_box<kNone, true, int16_t, TallCfg<int16_t>>(mode, d_mov, mdims, A, 1, p, s, launched);
         if (launched) {
             g_last_path = 4;
+            return rc;
+        }
+        rc = mov_dtype == MIA_F32 ? try_tile_box<kNone, true, float, DeepCfg<float>>(mode, d_mov, mdims, A, 1, p, s, launched)
+                                  : try_tile_box<kNone, true, int16_t, DeepCfg<int16_t>>(mode, d_mov, mdims, A, 1, p, s, launched);
+        if (launched) {
+            g_last_path = 7;
+            return rc;
+        }
+        rc = mov_dtype == MIA_F32 ? try_tile_box<kNone, true, float, CubeCfg<float>>(mode, d_mov, mdims, A, 1, p, s, launched)
+                                  : try_tile_box<kNone, true, int16_t, CubeCfg<int16_t>>(mode, d_mov, mdims, A, 1, p, s, launched);
+        if (launched) {
+            g_last_path = 8;
             return rc;
         }
     }

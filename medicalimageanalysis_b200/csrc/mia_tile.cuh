@@ -346,6 +346,10 @@ __device__ __forceinline__ void red_shared_inc(uint32_t addr)
     asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(addr) : "memory");
 }
 
+// (Warp-aggregated counter updates -- one MATCH.ALL per voxel, a single lane adding 32 when the whole warp lands in one
+// bin pair, as it does in air -- were built and measured on the config-3 phantoms: 51.4 us per evaluation against
+// 45.7 with plain per-lane atomics, same histogram.  The match costs more than the serialised wavefronts it removes.)
+
 // Per-thread constants of a launch: (lane * A[:,0] + warp * A[:,1]) in Q31.32 and the z column in float32.
 struct ThreadGeom {
     long long ox, oy, oz;

@@ -314,3 +314,28 @@ def test_large_in_plane_rotations_take_the_tall_box(cuda_device, dtype, mode, an
         # lerps of taps of that magnitude carry ~5e-4 of absolute rounding whatever the kernel
         assert not ((d > 1e-4 * np.maximum(np.abs(want.astype(np.float64)), 10.0)) & ~near).any()
     assert near.mean() < 0.02
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [np.int16, np.float32])
+@pytest.mark.parametrize("angles", [(15, 0, 0), (30, 0, 0), (45, 0, 0), (90, 0, 0), (0, 15, 0), (0, 30, 0), (0, 45, 0), (0, 90, 0),
+                                    (0, 0, 15), (0, 0, 30), (0, 0, 45), (0, 0, 90), (20, -15, 10)])
+def test_no_single_axis_rotation_falls_to_the_per_voxel_kernel(cuda_device, dtype, angles):
+    """Rigid.update_rotation takes any Euler triple (structure/rigid.py:950-974).  Rotations about z run on the tall box
+    family, about y on the z-heavy one, about x and moderate compound rotations on the cube -- never on the per-voxel
+    gather (path 0) -- and all of them match the oracle."""
+    shape, sp = (64, 72, 96), (1.0, 1.0, 1.0)
+    g = G.Grid((shape[2], shape[1], shape[0]), sp, tuple(-0.5 * np.array(sp) * np.array(shape[::-1])))
+    mov = make_phantom(shape, "CT", seed=31, spacing=sp).astype(dtype)
+    M = G.params_to_matrix(list(angles) + [2.0, -1.0, 1.5], (0, 0, 0))
+    for mode in ("vtk", "itk"):
+        A = G.compose_index_matrix(g, g, M, convention=mode)
+        got = kernels.resample(torch.from_numpy(mov).to(cuda_device), A, shape, background=BG[mode], mode=mode).cpu().numpy()
+        assert _lib.load().mia_debug_last_path() in (1, 4, 5, 7, 8), angles
+        want = reslice.oracle_reslice(mov, A, g.dims, BG[mode], mode, mov.dtype)
+        near = border_band(A, g.dims, g.dims)
+        d = np.abs(got.astype(np.float64) - want.astype(np.float64))
+        if dtype == np.int16:
+            assert not ((d > 1) & ~near).any()
+        else:
+            assert not ((d > 1e-4 * np.maximum(np.abs(want.astype(np.float64)), 10.0)) & ~near).any()
