@@ -261,6 +261,23 @@ def sharded_registration_extra(torch, dist, dev, world, rank, peak):
                 "note": "hbm_frac_per_eval counts 4 B per voxel per probe although the 13 probes of a launch share one "
                         "staged box and one read of the fixed image (L2 / shared-memory amortised: not HBM utilisation); "
                         "the launch-level fraction counts N_o*b_f + 13*N_m*b_m per launch"})
+    if world > 1:
+        try:
+            cfgf = RegistrationConfig(metric="ssd", iterations=50, graph_iters=10, collective="fused")
+            parallel.register_rigid_sharded(f, m, cfg=RegistrationConfig(metric="ssd", iterations=12, graph_iters=10, collective="fused"))
+            torch.cuda.synchronize(dev)
+            dist.barrier()
+            e0.record()
+            resf = parallel.register_rigid_sharded(f, m, cfg=cfgf)
+            e1.record()
+            torch.cuda.synchronize(dev)
+            dtf = _sync_max(torch, dist, dev, world, e0.elapsed_time(e1) * 1e-3)
+            out["fused_exchange"] = {"iters_per_s": resf.iterations / dtf,
+                                     "same_accept_reject_sequence": bool(np.array_equal(res.scale_history, resf.scale_history)),
+                                     "cost_rel_diff_max": float(np.max(np.abs(res.cost_history - resf.cost_history) / np.abs(res.cost_history))),
+                                     "nvlink_bytes_per_iteration_per_rank": 216 * world}
+        except Exception as exc:
+            out["fused_exchange"] = {"error": repr(exc)}
     Data.clear()
     del fixed, moving, f, m
     torch.cuda.empty_cache()
@@ -346,26 +363,40 @@ def c3_pair(dev):
 
 def probe_parallel_extra(torch, dist, dev, world):
     """Config 3 (256^3 float32 CT -> MR, 64-bin MI, 200 iterations) with the 13 probes of every iteration dealt out
-    over the ranks (the volume is too small for z-slabs): ONE all-reduce of 26 float64 per iteration, ten
-    iterations per CUDA graph.  Collective: every rank calls it."""
+    over the ranks (the volume is too small for z-slabs), ten iterations per CUDA graph, with both
+    exchanges: ONE NCCL all-reduce of 26 float64 per iteration, and the fused exchange (partials pushed into the peers'
+    symmetric buffers over NVLink, the device step waits on flags: no NCCL call).  Collective: every rank calls it."""
     from medicalimageanalysis_b200 import Data, RegistrationConfig, parallel
     f3, m3, gt3, _, _ = c3_pair(dev)
-    parallel.register_rigid_probe_parallel(f3, m3, cfg=RegistrationConfig(metric="mi", iterations=21, bins=64, graph_iters=10))
-    torch.cuda.synchronize(dev)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    if world > 1:
-        dist.barrier()
-    e0.record()
-    res = parallel.register_rigid_probe_parallel(f3, m3, cfg=RegistrationConfig(metric="mi", iterations=200, bins=64, graph_iters=10))
-    e1.record()
-    torch.cuda.synchronize(dev)
-    dt = _sync_max(torch, dist, dev, world, e0.elapsed_time(e1) * 1e-3)
+    out = {"n_gpus": world, "gt_params": list(gt3)}
+    ref = None
+    for coll in ("nccl", "fused"):
+        try:
+            parallel.register_rigid_probe_parallel(f3, m3, cfg=RegistrationConfig(metric="mi", iterations=21, bins=64,
+                                                                                 graph_iters=10, collective=coll))
+            torch.cuda.synchronize(dev)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            if world > 1:
+                dist.barrier()
+            e0.record()
+            res = parallel.register_rigid_probe_parallel(f3, m3, cfg=RegistrationConfig(metric="mi", iterations=200, bins=64,
+                                                                                       graph_iters=10, collective=coll))
+            e1.record()
+            torch.cuda.synchronize(dev)
+            dt = _sync_max(torch, dist, dev, world, e0.elapsed_time(e1) * 1e-3)
+            out[coll] = {"iters_per_s": res.iterations / dt, "evals_per_s": res.evaluations / dt,
+                         "final_params": [round(float(v), 3) for v in res.params]}
+            if ref is None:
+                ref = res
+            else:
+                out["fused_trajectory_identical_to_nccl"] = _all_true(torch, dist, dev, world, bool(
+                    np.array_equal(ref.cost_history, res.cost_history) and np.array_equal(ref.params, res.params)))
+        except Exception as exc:
+            out[coll] = {"error": repr(exc)}
     Data.clear()
-    return {"iters_per_s": res.iterations / dt, "evals_per_s": res.evaluations / dt, "n_gpus": world,
-            "final_params": [round(float(v), 3) for v in res.params], "gt_params": list(gt3),
-            "note": "13 probes per iteration dealt out over the ranks, volumes replicated, ONE all_reduce(SUM) of "
-                    "{mi,count}[13] (208 B) per iteration, 10 iterations per CUDA graph"}
-
+    out["note"] = ("13 probes per iteration dealt out over the ranks, volumes replicated, 208 B exchanged per iteration and "
+                   "rank, 10 iterations per CUDA graph")
+    return out
 
 
 def cpu_reslice_runs(mov, A, dims, runs, warm=1):

@@ -146,6 +146,21 @@ int mia_metric_pack(const double *d_metric, const unsigned long long *d_count, i
                     double *d_packed, void *stream);
 int mia_optimizer_step_packed(void *d_state, const double *d_packed, int metric_is_ssd, double *d_A, double *d_A_slab,
                               int k0, void *stream);
+/*
+ * The exchange of those 26 doubles WITHOUT a collective library call ("mia_allreduce_fused").  Every
+ * rank owns a buffer of mia_fused_exchange_bytes() in symmetric, peer-mapped memory (zeroed, then a host barrier, before
+ * the first use; e.g. torch.distributed._symmetric_memory).  mia_fused_push stores this rank's packed partials into slot
+ * [parity][rank] of EVERY rank's buffer through NVLink (d_peer_bufs: device array of `world` buffer pointers, own one
+ * included), fences and raises its flag in every buffer; mia_optimizer_step_fused waits for the `world` flags of the
+ * iteration, adds the slots in rank order and steps as mia_optimizer_step_packed does.  Two small launches per
+ * iteration, no host involvement, capturable.  A wait gives up after about two seconds (a dead peer must not hang the
+ * GPU) and counts the event; mia_fused_timeouts reads the counter back (synchronises): non-zero = results invalid.
+ */
+size_t mia_fused_exchange_bytes(void);
+int mia_fused_push(const void *d_state, const double *d_packed, void *const *d_peer_bufs, int rank, int world, void *stream);
+int mia_optimizer_step_fused(void *d_state, void *d_my_buf, int world, int metric_is_ssd, double *d_A, double *d_A_slab,
+                             int k0, void *stream);
+int mia_fused_timeouts(const void *d_my_buf, unsigned long long *timeouts, void *stream);
 /* Copy the optimiser state back (synchronises `stream`).  Any output pointer may be NULL; hist_* hold
  * min(iters, max_hist) entries: the centre cost, parameters [n][6] and step scale seen at each step. */
 int mia_optimizer_read(const void *d_state, double params[6], double *scale, int *iters, int *converged,

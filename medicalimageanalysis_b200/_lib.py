@@ -60,6 +60,10 @@ SIGNATURES = {
     "mia_shrink_mean": (_i, [_vp, _i, _ip, _vp, _ip, _vp]),
     "mia_metric_pack": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
     "mia_optimizer_step_packed": (_i, [_vp, _vp, _i, _vp, _vp, _i, _vp]),
+    "mia_fused_exchange_bytes": (_sz, []),
+    "mia_fused_push": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
+    "mia_optimizer_step_fused": (_i, [_vp, _vp, _i, _i, _vp, _vp, _i, _vp]),
+    "mia_fused_timeouts": (_i, [_vp, _c.POINTER(_c.c_ulonglong), _vp]),
     "mia_host_register": (_i, [_vp, _sz]),
     "mia_host_unregister": (_i, [_vp]),
     "mia_host_alloc": (_vp, [_sz]),

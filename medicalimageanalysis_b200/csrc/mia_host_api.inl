@@ -207,6 +207,39 @@ int mia_optimizer_step_packed(void *d_state, const double *d_packed, int metric_
     return MIA_OK;
 }
 
+size_t mia_fused_exchange_bytes(void) { return (sizeof(FusedBuf) + 255) & ~(size_t)255; }
+
+int mia_fused_push(const void *d_state, const double *d_packed, void *const *d_peer_bufs, int rank, int world, void *stream)
+{
+    if (!d_state || !d_packed || !d_peer_bufs) return fail(MIA_ERR_ARG, "mia_fused_push: null pointer");
+    if (world < 1 || world > kFusedMaxWorld || rank < 0 || rank >= world)
+        return fail(MIA_ERR_ARG, "mia_fused_push: need 0 <= rank < world <= %d", kFusedMaxWorld);
+    fused_push_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(static_cast<const OptState *>(d_state), d_packed,
+                                                          reinterpret_cast<FusedBuf *const *>(d_peer_bufs), rank, world);
+    CUDA_TRY(cudaGetLastError());
+    return MIA_OK;
+}
+
+int mia_optimizer_step_fused(void *d_state, void *d_my_buf, int world, int metric_is_ssd, double *d_A, double *d_A_slab,
+                             int k0, void *stream)
+{
+    if (!d_state || !d_my_buf || !d_A) return fail(MIA_ERR_ARG, "mia_optimizer_step_fused: null pointer");
+    if (world < 1 || world > kFusedMaxWorld) return fail(MIA_ERR_ARG, "mia_optimizer_step_fused: world must be 1..%d", kFusedMaxWorld);
+    optimizer_step_fused_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(static_cast<OptState *>(d_state), static_cast<FusedBuf *>(d_my_buf),
+                                                                   world, metric_is_ssd, d_A, d_A_slab, k0);
+    CUDA_TRY(cudaGetLastError());
+    return MIA_OK;
+}
+
+int mia_fused_timeouts(const void *d_my_buf, unsigned long long *timeouts, void *stream)
+{
+    if (!d_my_buf || !timeouts) return fail(MIA_ERR_ARG, "mia_fused_timeouts: null pointer");
+    CUDA_TRY(cudaMemcpyAsync(timeouts, &static_cast<const FusedBuf *>(d_my_buf)->timeouts, sizeof(unsigned long long),
+                             cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+    return MIA_OK;
+}
+
 int mia_optimizer_read(const void *d_state, double params[6], double *scale, int *iters, int *converged,
                        int *n_reject, double *hist_cost, double *hist_params, double *hist_scale,
                        int max_hist, void *stream)

@@ -98,10 +98,9 @@ __global__ void optimizer_init_kernel(OptState *st, double *dA)
 // loops).  dA_slab, when given, receives the same probes shifted to a z-slab that starts at fixed plane k0
 // (A[:, 3] += A[:, 2] * k0): the sharded loop then needs no kernel of its own for the shift.
 template <typename CNT>
-__global__ void optimizer_step_kernel(OptState *st, const double *metric, const CNT *count, int metric_is_ssd, double *dA,
-                                      double *dA_slab = nullptr, int k0 = 0)
+__device__ inline void opt_step(OptState *st, const double *metric, const CNT *count, int metric_is_ssd, double *dA,
+                                double *dA_slab, int k0)
 {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
     double c[kOptProbes];
     for (int q = 0; q < kOptProbes; ++q) {
         if (metric_is_ssd) {
@@ -145,6 +144,71 @@ __global__ void optimizer_step_kernel(OptState *st, const double *metric, const 
     }
     opt_emit_probes(st, dA);
     if (dA_slab) opt_shift_probes(dA, dA_slab, k0);
+}
+
+template <typename CNT>
+__global__ void optimizer_step_kernel(OptState *st, const double *metric, const CNT *count, int metric_is_ssd, double *dA,
+                                      double *dA_slab = nullptr, int k0 = 0)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    opt_step<CNT>(st, metric, count, metric_is_ssd, dA, dA_slab, k0);
+}
+
+// ---- fused exchange over NVLink peer memory ------------------------------------------------------
+// Every rank owns one FusedBuf in symmetric memory (same layout on every GPU, peer-mapped).  Per iteration, rank r
+// stores its 26 packed doubles into slot [parity][r] of EVERY rank's buffer (plain stores through NVLink), fences, and
+// then writes the iteration number into flag [parity][r] of every rank.  The optimiser step on each rank waits until
+// all `world` flags of the parity carry the iteration number, adds the slots in rank order (deterministic, identical on
+// every rank) and steps.  No NCCL call, no host involvement: two small kernels per iteration, capturable.
+// Parity = iteration & 1 is enough: a rank can only write iteration n + 1 after its own step n, which needed every
+// peer's flag n, which a peer writes only after it finished reading iteration n - 1 (the previous use of that parity).
+constexpr int kFusedMaxWorld = 16;
+
+struct FusedBuf {
+    double data[2][kFusedMaxWorld][2 * kOptProbes];
+    unsigned long long flag[2][kFusedMaxWorld];
+    unsigned long long timeouts;          // number of waits that gave up (a peer never arrived): results are then invalid
+};
+
+__global__ void fused_push_kernel(const OptState *st, const double *packed_local, FusedBuf *const *peers, int rank, int world)
+{
+    const unsigned long long seq = (unsigned long long)st->iter + 1ull;
+    const int par = (int)(seq & 1ull);
+    constexpr int n = 2 * kOptProbes;
+    for (int t = threadIdx.x; t < n * world; t += blockDim.x) peers[t / n]->data[par][rank][t % n] = packed_local[t % n];
+    __threadfence_system();               // this thread's payload stores are visible system-wide before any flag is
+    __syncthreads();
+    if ((int)threadIdx.x < world) {
+        volatile unsigned long long *f = &peers[threadIdx.x]->flag[par][rank];
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(f), "l"(seq) : "memory");
+    }
+}
+
+__global__ void optimizer_step_fused_kernel(OptState *st, FusedBuf *mine, int world, int metric_is_ssd, double *dA,
+                                            double *dA_slab, int k0)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const unsigned long long seq = (unsigned long long)st->iter + 1ull;
+    const int par = (int)(seq & 1ull);
+    const long long t0 = clock64();
+    for (int r = 0; r < world; ++r) {
+        const unsigned long long *f = &mine->flag[par][r];
+        unsigned long long v;
+        do {
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+            if (v != seq && clock64() - t0 > 4000000000ll) {       // ~2 s at 2 GHz: a peer is gone; do not hang the GPU
+                mine->timeouts += 1ull;
+                break;
+            }
+        } while (v != seq);
+    }
+    double packed[2 * kOptProbes];
+    for (int i = 0; i < 2 * kOptProbes; ++i) {
+        double s = 0.0;
+        for (int r = 0; r < world; ++r) s += *(volatile const double *)&mine->data[par][r][i];
+        packed[i] = s;
+    }
+    opt_step<double>(st, packed, packed + kOptProbes, metric_is_ssd, dA, dA_slab, k0);
 }
 
 // packed[0 .. n_total) = metric, packed[n_total .. 2 n_total) = (double)count, both zero outside this rank's share

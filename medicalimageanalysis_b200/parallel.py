@@ -158,6 +158,34 @@ def resample_host_slab(h_moving, A, h_out, rank, world, background=-3001.0, mode
     return (k0, k1), (z0, z1)
 
 
+class FusedExchange(object):
+    """Symmetric, peer-mapped buffers for the collective-free exchange of the 26 packed doubles of an iteration
+    (``mia_fused_push`` / ``mia_optimizer_step_fused``).  One ``FusedBuf`` per rank from
+    ``torch.distributed._symmetric_memory``; zeroed, then a barrier, so that no rank can see a stale flag.  NVLink
+    traffic per iteration and rank: ``world`` x (208 B payload + 8 B flag) of peer stores."""
+
+    def __init__(self, lib, device, group=None):
+        import torch
+        import torch.distributed._symmetric_memory as symm_mem
+        dist = _dist()
+        self.lib = lib
+        self.group = group if group is not None else dist.group.WORLD
+        n = int(lib.mia_fused_exchange_bytes()) // 8
+        self.buf = symm_mem.empty(n, dtype=torch.float64, device=device)
+        self.buf.zero_()
+        self.handle = symm_mem.rendezvous(self.buf, self.group)
+        self.rank, self.world = int(self.handle.rank), int(self.handle.world_size)
+        self.peers = torch.tensor([int(p) for p in self.handle.buffer_ptrs], dtype=torch.int64, device=device)
+        torch.cuda.synchronize(device)
+        dist.barrier(group=group)
+
+    def timeouts(self, stream):
+        t = ctypes.c_ulonglong(0)
+        from . import _lib
+        _lib.check(self.lib.mia_fused_timeouts(self.buf.data_ptr(), ctypes.byref(t), stream))
+        return int(t.value)
+
+
 def _loop_and_read(lib, _lib, torch, dev, cfg, state, one_iteration, center, extra):
     """Run ``cfg.iterations`` of ``one_iteration`` on the current stream -- ``cfg.graph_iters`` at a time as a replayed
     CUDA graph when asked (NCCL collectives are capturable; every rank captures the same sequence) -- and read the
@@ -260,6 +288,12 @@ def register_rigid_sharded(fixed, moving, params0=None, cfg=None, group=None):
     def stream():
         return ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
 
+    fused = None
+    if cfg.collective == "fused" and world > 1 and is_ssd:      # MI by z-slab reduces 213 KB of histograms: NCCL's job
+        fused = FusedExchange(lib, dev, group)
+    elif cfg.collective not in ("nccl", "fused"):
+        raise ValueError("collective must be 'nccl' or 'fused'")
+
     with torch.cuda.device(dev):
         _lib.check(lib.mia_optimizer_init(state.data_ptr(), _lib.darr(params0), _lib.darr(center),
                                           _lib.darr(p2w.ravel()), _lib.darr(w2p.ravel()), cfg.rot_step_deg,
@@ -275,7 +309,8 @@ def register_rigid_sharded(fixed, moving, params0=None, cfg=None, group=None):
                                                    packed.data_ptr(), stream()))
                 else:
                     _lib.check(lib.mia_metric_pack(None, None, 0, 0, N_PROBES, packed.data_ptr(), stream()))
-                all_reduce_sum(packed, group=group)
+                if fused is None:
+                    all_reduce_sum(packed, group=group)
             else:
                 if slab is not None:
                     kernels.resample_jointhist(slab, moving.array, frange, mrange, bins=cfg.bins, d_A=d_Aloc,
@@ -285,10 +320,19 @@ def register_rigid_sharded(fixed, moving, params0=None, cfg=None, group=None):
                 all_reduce_sum(hist_i32, group=group)
                 kernels.mi_from_hist(ws.hist, out=ws.mi)
                 _lib.check(lib.mia_metric_pack(ws.mi.data_ptr(), None, N_PROBES, 0, N_PROBES, packed.data_ptr(), stream()))
-            _lib.check(lib.mia_optimizer_step_packed(state.data_ptr(), packed.data_ptr(), 1 if is_ssd else 0,
-                                                     d_A.data_ptr(), d_Aloc.data_ptr(), int(k0), stream()))
+            if fused is not None and is_ssd:
+                _lib.check(lib.mia_fused_push(state.data_ptr(), packed.data_ptr(), fused.peers.data_ptr(), rank, world, stream()))
+                _lib.check(lib.mia_optimizer_step_fused(state.data_ptr(), fused.buf.data_ptr(), world, 1, d_A.data_ptr(),
+                                                        d_Aloc.data_ptr(), int(k0), stream()))
+            else:
+                _lib.check(lib.mia_optimizer_step_packed(state.data_ptr(), packed.data_ptr(), 1 if is_ssd else 0,
+                                                         d_A.data_ptr(), d_Aloc.data_ptr(), int(k0), stream()))
 
-        return _loop_and_read(lib, _lib, torch, dev, cfg, state, one_iteration, center, {"slab": (k0, k1), "world": world})
+        res = _loop_and_read(lib, _lib, torch, dev, cfg, state, one_iteration, center,
+                             {"slab": (k0, k1), "world": world, "collective": "fused" if fused is not None else "nccl"})
+        if fused is not None and fused.timeouts(stream()):
+            raise RuntimeError("fused exchange: a peer never arrived (timeout); the result is invalid")
+        return res
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -360,6 +404,10 @@ def register_rigid_probe_parallel(fixed, moving, params0=None, cfg=None, group=N
     def stream():
         return ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
 
+    if cfg.collective not in ("nccl", "fused"):
+        raise ValueError("collective must be 'nccl' or 'fused'")
+    fused = FusedExchange(lib, dev, group) if (cfg.collective == "fused" and world > 1) else None
+
     with torch.cuda.device(dev):
         _lib.check(lib.mia_optimizer_init(state.data_ptr(), _lib.darr(params0), _lib.darr(center),
                                           _lib.darr(p2w.ravel()), _lib.darr(w2p.ravel()), cfg.rot_step_deg,
@@ -378,8 +426,17 @@ def register_rigid_probe_parallel(fixed, moving, params0=None, cfg=None, group=N
                 _lib.check(lib.mia_metric_pack(v.data_ptr(), c.data_ptr(), nloc, q0, N_PROBES, packed.data_ptr(), stream()))
             else:
                 _lib.check(lib.mia_metric_pack(None, None, 0, 0, N_PROBES, packed.data_ptr(), stream()))
-            all_reduce_sum(packed, group=group)
-            _lib.check(lib.mia_optimizer_step_packed(state.data_ptr(), packed.data_ptr(), 1 if is_ssd else 0,
-                                                     d_A.data_ptr(), None, 0, stream()))
+            if fused is not None:
+                _lib.check(lib.mia_fused_push(state.data_ptr(), packed.data_ptr(), fused.peers.data_ptr(), rank, world, stream()))
+                _lib.check(lib.mia_optimizer_step_fused(state.data_ptr(), fused.buf.data_ptr(), world, 1 if is_ssd else 0,
+                                                        d_A.data_ptr(), None, 0, stream()))
+            else:
+                all_reduce_sum(packed, group=group)
+                _lib.check(lib.mia_optimizer_step_packed(state.data_ptr(), packed.data_ptr(), 1 if is_ssd else 0,
+                                                         d_A.data_ptr(), None, 0, stream()))
 
-        return _loop_and_read(lib, _lib, torch, dev, cfg, state, one_iteration, center, {"probes": (q0, q1), "world": world})
+        res = _loop_and_read(lib, _lib, torch, dev, cfg, state, one_iteration, center,
+                             {"probes": (q0, q1), "world": world, "collective": "fused" if fused is not None else "nccl"})
+        if fused is not None and fused.timeouts(stream()):
+            raise RuntimeError("fused exchange: a peer never arrived (timeout); the result is invalid")
+        return res

@@ -38,6 +38,8 @@ class RegistrationConfig:
     frange: tuple | None = None      # intensity ranges for MI; None -> from the volumes, once
     mrange: tuple | None = None
     graph_iters: int = 10            # iterations captured per CUDA graph (0 = no graph)
+    collective: str = "nccl"         # sharded loops: "nccl" (one all_reduce per iteration) or "fused" (partials pushed into
+                                     # the peers' symmetric buffers over NVLink, the device step waits on flags: no NCCL call)
     fixed_mask: object = None        # uint8 CUDA tensor on the fixed lattice (SetMetricFixedMask); None = all voxels
     moving_mask: object = None       # same on the moving lattice (SetMetricMovingMask); runs the per-voxel kernel
 
