@@ -164,20 +164,38 @@ class FusedExchange(object):
     ``torch.distributed._symmetric_memory``; zeroed, then a barrier, so that no rank can see a stale flag.  NVLink
     traffic per iteration and rank: ``world`` x (208 B payload + 8 B flag) of peer stores."""
 
+    _cache = {}      # (device index, group) -> FusedExchange: allocation + rendezvous cost tens of milliseconds, once
+
+    @classmethod
+    def get(cls, lib, device, group=None):
+        """The exchange of (device, group), created on first use; every use starts from zeroed flags behind a barrier."""
+        import torch
+        key = (torch.device(device).index, group)
+        ex = cls._cache.get(key)
+        if ex is None:
+            ex = cls._cache[key] = cls(lib, device, group)
+        ex.reset()
+        return ex
+
     def __init__(self, lib, device, group=None):
         import torch
         import torch.distributed._symmetric_memory as symm_mem
         dist = _dist()
-        self.lib = lib
+        self.lib, self.device, self.group_arg = lib, device, group
         self.group = group if group is not None else dist.group.WORLD
         n = int(lib.mia_fused_exchange_bytes()) // 8
         self.buf = symm_mem.empty(n, dtype=torch.float64, device=device)
-        self.buf.zero_()
         self.handle = symm_mem.rendezvous(self.buf, self.group)
         self.rank, self.world = int(self.handle.rank), int(self.handle.world_size)
         self.peers = torch.tensor([int(p) for p in self.handle.buffer_ptrs], dtype=torch.int64, device=device)
-        torch.cuda.synchronize(device)
-        dist.barrier(group=group)
+
+    def reset(self):
+        """A new loop counts its iterations from 1 again: clear the flags of the previous one.  Every rank has left its
+        previous loop (it ends with a synchronising read-back), zeroes its OWN buffer, and only then meets the others."""
+        import torch
+        self.buf.zero_()
+        torch.cuda.synchronize(self.device)
+        _dist().barrier(group=self.group_arg)
 
     def timeouts(self, stream):
         t = ctypes.c_ulonglong(0)
@@ -290,7 +308,7 @@ def register_rigid_sharded(fixed, moving, params0=None, cfg=None, group=None):
 
     fused = None
     if cfg.collective == "fused" and world > 1 and is_ssd:      # MI by z-slab reduces 213 KB of histograms: NCCL's job
-        fused = FusedExchange(lib, dev, group)
+        fused = FusedExchange.get(lib, dev, group)
     elif cfg.collective not in ("nccl", "fused"):
         raise ValueError("collective must be 'nccl' or 'fused'")
 
@@ -406,7 +424,7 @@ def register_rigid_probe_parallel(fixed, moving, params0=None, cfg=None, group=N
 
     if cfg.collective not in ("nccl", "fused"):
         raise ValueError("collective must be 'nccl' or 'fused'")
-    fused = FusedExchange(lib, dev, group) if (cfg.collective == "fused" and world > 1) else None
+    fused = FusedExchange.get(lib, dev, group) if (cfg.collective == "fused" and world > 1) else None
 
     with torch.cuda.device(dev):
         _lib.check(lib.mia_optimizer_init(state.data_ptr(), _lib.darr(params0), _lib.darr(center),
