@@ -304,8 +304,8 @@ template <class BOX, int NST>
 struct X2Smem {
     static constexpr unsigned kBoxBytes = BOX::kX * BOX::kY * BOX::kZ * 2u;
     static constexpr unsigned kStageBytes = (kBoxBytes + 127u) & ~127u;
-    static constexpr unsigned kBarOff = kStageBytes * NST;
-    static constexpr unsigned kInfoOff = kBarOff + 16u * NST;
+    static constexpr unsigned kBarOff = kStageBytes * NST;                 // full[NST], empty[NST], info_full[2], info_empty[2]
+    static constexpr unsigned kInfoOff = kBarOff + 16u * NST + 32u;
     static constexpr unsigned kBytes = kInfoOff + (unsigned)sizeof(TileInfo) * 64u;
 };
 
@@ -327,10 +327,25 @@ tile_x2_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
 #pragma unroll
         for (int q = 0; q < 12; ++q) A[q] = Ap[q];
     }
+    // Tile records travel in passes of 32 (two passes resident) behind their own barrier pair, because only tiles that
+    // need a box take a ring slot: a tile outside the volume (18.6 % of config 2's tiles, the auto-crop corners) or one
+    // too large for the box costs the ring nothing, so the box of the tile AFTER it is requested as soon as a slot is
+    // free instead of one (very short) tile ahead (206 -> 203 us on config 2).
+    //
+    // Tried and dropped: ONE CTA per SM with two groups of 8 consumer warps around one shared 4-stage ring, tiles
+    // claimed dynamically (one shared-memory atomic + a named barrier per group and tile): 213 us.  The consumers'
+    // quarter of their time on the full barrier is mostly skew between the 8 warps of a tile (interior, border and dead
+    // rows in one tile), not late boxes -- L2 -> SM runs at 45 % of its cap -- and a barrier per tile removes the
+    // little slack a ring leaves them.
+    const uint32_t ibar = bar0 + 16 * NST;                  // info_full[b] = ibar + 8 b, info_empty[b] = ibar + 16 + 8 b
     if (tid == 0) {
         for (int s = 0; s < NST; ++s) {
             mbar_init(bar0 + 8 * s, 1);
             mbar_init(bar0 + 8 * (NST + s), kX2Consumers);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(ibar + 8 * b, 1);
+            mbar_init(ibar + 16 + 8 * b, kX2Consumers);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -358,8 +373,12 @@ tile_x2_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
                 const int z = (int)(tile / (unsigned)txy), r2 = (int)(tile % (unsigned)txy);
                 mine = x2_classify<BOX>(A, reach, (r2 % p.ntx) * kXW, (r2 / p.ntx) * kXH, z * kXD, p.mov.nx, p.mov.ny, p.mov.nz);
             }
+            const int pass = base >> 5;
+            if (pass >= 2 && lane == 0) mbar_wait<200>(ibar + 16 + 8 * (pass & 1), (unsigned)(((pass - 2) >> 1) & 1));
+            __syncwarp();                                   // the consumers are done with the records of pass - 2
             infos[(base & 32) + lane] = mine;
             __syncwarp();
+            if (lane == 0) mbar_arrive(ibar + 8 * (pass & 1));
             const int cnt_pass = min(32, ntile_mine - base);
             for (int q = 0; q < cnt_pass; ++q) {
                 const int cls = __shfl_sync(0xffffffffu, mine.cls, q);
@@ -375,14 +394,11 @@ tile_x2_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
                         asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(&tmap), "r"(px), "r"(py), "r"(pz) : "memory");
                 }
 #endif
+                if (cls != kInterior && cls != kBorder) continue;          // no box, no ring slot
                 if (lane == 0) {
                     mbar_wait<200>(bar0 + 8 * (NST + s), ph ^ 1u);
-                    if (cls == kInterior || cls == kBorder) {
-                        mbar_arrive_expect_tx(bar0 + 8 * s, L::kBoxBytes);
-                        tma_load_3d(smem_u32(xsm + L::kStageBytes * s), &tmap, bar0 + 8 * s, bx, by, bz);
-                    } else {
-                        mbar_arrive(bar0 + 8 * s);
-                    }
+                    mbar_arrive_expect_tx(bar0 + 8 * s, L::kBoxBytes);
+                    tma_load_3d(smem_u32(xsm + L::kStageBytes * s), &tmap, bar0 + 8 * s, bx, by, bz);
                 }
                 if (++s == NST) { s = 0; ph ^= 1u; }
             }
@@ -399,18 +415,29 @@ tile_x2_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
             tiy += step_y;
             if (tiy >= p.nty) { tiy -= p.nty; ++tiz; }
             tiz += step_z;
-            mbar_wait<32>(bar0 + 8 * s, ph);
+            const int pass = n >> 5;
+            if ((n & 31) == 0) mbar_wait<32>(ibar + 8 * (pass & 1), (unsigned)((pass >> 1) & 1));      // records of this pass
             const TileInfo ti = infos[n & 63];
-            const uint32_t stage = smem_u32(xsm + L::kStageBytes * s);
-            int cls = ti.cls;
-            if (cls == kBorder) cls = x2_refine<VTK>(p, ti, geom, i0, j0, lane, warp);
-            if (cls == kInterior) x2_tile<VTK, false, BOX>(p, stage, ti, geom, i0, j0, k0, lane, warp);
-            else if (cls == kBorder) x2_tile<VTK, true, BOX>(p, stage, ti, geom, i0, j0, k0, lane, warp);
-            else if (cls == kOutside) x2_fill_background<VTK>(p, i0, j0, k0, lane, warp);
-            else x2_tile_nobox<VTK>(p, p.dA ? p.dA : p.A0.a, i0, j0, k0, lane, warp);
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar0 + 8 * (NST + s));
-            if (++s == NST) { s = 0; ph ^= 1u; }
+            if (ti.cls == kInterior || ti.cls == kBorder) {
+                mbar_wait<32>(bar0 + 8 * s, ph);
+                const uint32_t stage = smem_u32(xsm + L::kStageBytes * s);
+                int cls = ti.cls;
+                if (cls == kBorder) cls = x2_refine<VTK>(p, ti, geom, i0, j0, lane, warp);
+                if (cls == kInterior) x2_tile<VTK, false, BOX>(p, stage, ti, geom, i0, j0, k0, lane, warp);
+                else if (cls == kBorder) x2_tile<VTK, true, BOX>(p, stage, ti, geom, i0, j0, k0, lane, warp);
+                else x2_fill_background<VTK>(p, i0, j0, k0, lane, warp);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar0 + 8 * (NST + s));
+                if (++s == NST) { s = 0; ph ^= 1u; }
+            } else if (ti.cls == kOutside) {
+                x2_fill_background<VTK>(p, i0, j0, k0, lane, warp);
+            } else {
+                x2_tile_nobox<VTK>(p, p.dA ? p.dA : p.A0.a, i0, j0, k0, lane, warp);
+            }
+            if ((n & 31) == 31 || n == ntile_mine - 1) {
+                __syncwarp();
+                if (lane == 0) mbar_arrive(ibar + 16 + 8 * (pass & 1));
+            }
         }
     }
 
