@@ -52,6 +52,12 @@ const char *mia_last_error(void);
  * 4 / 7 / 8 = the tile kernel with the tall / deep / cube box family, 5 = x-pair tile kernel, 6 = x-pair multi-matrix
  * kernel).  Used by the parity tests. */
 int mia_debug_last_path(void);
+/* Diagnostic / escape hatch: the x-pair kernel hands its tiles out through a per-launch claim counter (CTAs that drew
+ * cheap tiles take more of them).  on != 0 keeps the static round-robin order instead (the same voxels either way,
+ * bit for bit); the environment variable MIA_X2_STATIC=1 sets the initial state.  Needed only by a caller that runs
+ * two executable instances of ONE captured graph concurrently.  Returns the previous setting.  No counterpart in the
+ * reference. */
+int mia_debug_x2_static(int on);
 
 /*
  * Rigid trilinear resample of a device-resident moving volume onto an output lattice.

@@ -26,6 +26,7 @@ SIGNATURES = {
     "mia_version": (_i, []),
     "mia_last_error": (_c.c_char_p, []),
     "mia_debug_last_path": (_i, []),
+    "mia_debug_x2_static": (_i, [_i]),
     "mia_resample_rigid": (_i, [_vp, _i, _ip, _vp, _i, _ip, _dp, _d, _i, _vp]),
     "mia_resample_rigid_host": (_i, [_vp, _i, _ip, _vp, _i, _ip, _dp, _d, _i, _i]),
     "mia_autocrop_extent": (_i, [_dp, _dp, _ip, _dp, _i, _ip, _dp]),

@@ -5,6 +5,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <atomic>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -577,6 +578,52 @@ bool x2_box_fits(const double *A)
     return true;
 }
 
+// Claim counters of the x-pair kernel's dynamic tile order: {next tile, CTAs done} per launch, zero when idle (the last
+// CTA of a launch zeroes its pair).  A launch in flight must own its pair, so
+//   * eager launches walk a pool of kX2EagerSlots pairs in launch order: two launches share a pair only when they are
+//     kX2EagerSlots launches apart, far beyond what the launch queues of a process hold in flight;
+//   * a launch under stream capture runs again with every replay of its graph, at any later time: it takes a pair
+//     of its own out of a second pool for good (a replay cannot overlap itself: launches of one executable graph are
+//     ordered).  When that pool is used up, captured launches keep the static round-robin order (claim == nullptr).
+// MIA_X2_STATIC=1 keeps the static order everywhere (e.g. for two executable instances of ONE captured graph that are
+// to run concurrently on two streams).
+constexpr unsigned kX2EagerSlots = 1u << 16, kX2GraphSlots = 1u << 16;
+std::atomic<int> g_x2_static{[] { const char *e = getenv("MIA_X2_STATIC"); return e && *e && *e != '0' ? 1 : 0; }()};
+__device__ unsigned g_x2_claims[kX2EagerSlots + kX2GraphSlots][2];
+
+int x2_claim_slot(cudaStream_t s, unsigned **claim)
+{
+    *claim = nullptr;
+    if (g_x2_static.load()) return MIA_OK;
+    static std::mutex mu;
+    static unsigned *base[64] = {nullptr};
+    static std::atomic<unsigned> seq_eager{0}, seq_graph{0};
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return MIA_OK;
+    unsigned *b = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!base[dev]) {
+            void *ptr = nullptr;
+            CUDA_TRY(cudaGetSymbolAddress(&ptr, g_x2_claims));
+            base[dev] = static_cast<unsigned *>(ptr);
+        }
+        b = base[dev];
+    }
+    if (!b) return MIA_OK;
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    CUDA_TRY(cudaStreamIsCapturing(s, &st));
+    if (st == cudaStreamCaptureStatusNone) {
+        *claim = b + 2u * (seq_eager.fetch_add(1u) % kX2EagerSlots);
+    } else {
+        const unsigned slot = seq_graph.fetch_add(1u);
+        if (slot < kX2GraphSlots) *claim = b + 2u * (kX2EagerSlots + slot);
+        else seq_graph.store(kX2GraphSlots);               // stay saturated instead of wrapping
+    }
+    return MIA_OK;
+}
+
 template <bool VTK>
 int launch_x2(const CUtensorMap &map, const KParams &p, cudaStream_t s)
 {
@@ -603,10 +650,14 @@ int launch_x2(const CUtensorMap &map, const KParams &p, cudaStream_t s)
     }
     static const int maxb = [] { const char *e = getenv("MIA_X2_MAXB"); return e && *e ? atoi(e) : 0; }();   // tuning knob
     if (maxb > 0 && nb > maxb) nb = maxb;
+    const long long nchunks = (p.ntiles + kX2Pass - 1) / kX2Pass;
     long long gx = (long long)sm_count() * nb;
-    if (gx > p.ntiles) gx = p.ntiles;
+    if (gx > nchunks) gx = nchunks;
     if (gx > kMaxGridX) gx = kMaxGridX;
-    k<<<dim3((unsigned)gx, 1, 1), kX2Threads, smem, s>>>(map, p);
+    KParams q = p;
+    const int rc = x2_claim_slot(s, &q.ws_ticket);          // nullptr: chunks go round-robin
+    if (rc) return rc;
+    k<<<dim3((unsigned)gx, 1, 1), kX2Threads, smem, s>>>(map, q);
     CUDA_TRY(cudaGetLastError());
     g_last_path = 5;
     return MIA_OK;
@@ -650,6 +701,11 @@ int mia_version(void) { return MIA_B200_VERSION; }
 const char *mia_last_error(void) { return g_err.c_str(); }
 
 int mia_debug_last_path(void) { return g_last_path; }
+
+int mia_debug_x2_static(int on)
+{
+    return g_x2_static.exchange(on ? 1 : 0);
+}
 
 int mia_resample_rigid(const void *d_mov, int mov_dtype, const int mdims[3], void *d_out, int out_dtype,
                        const int odims[3], const double A[12], double background, int mode, void *stream)

@@ -25,15 +25,19 @@
 
 namespace mia {
 
-#ifndef MIA_X2_PREFETCH
-#define MIA_X2_PREFETCH 0      // tiles ahead of the ring that the producer prefetches into L2 (0 = off)
-#endif
+// (An L2 prefetch of the boxes a few tiles ahead of the ring, cp.async.bulk.prefetch.tensor, was measured: no gain.)
 // Registers: two CTAs of 9 warps put 5 warps on one scheduler, whose 16 K registers then allow 102 per thread --
 // __launch_bounds__(288, 2) makes ptxas stop at 96 (a cap of 112 through __maxnreg__ left ONE resident CTA: 248 us
 // instead of 209 on config 2).
 constexpr int kXW = 64, kXH = 8, kXD = 8;            // tile: x, y, z
 constexpr int kX2Consumers = kXH;
 constexpr int kX2Threads = 32 * (kX2Consumers + 1);
+#ifndef MIA_X2_PASS
+#define MIA_X2_PASS 4
+#endif
+constexpr int kX2Pass = MIA_X2_PASS;                    // tiles per claim = records per pass (two passes resident), <= 32.  Config 2 / its
+                                                        // z-slab of 8, same box: 16: 198 / 45 us, 8: 193 / 41, 4: 191 / 37, 2: 211 / 37, 1: 226 / 39
+constexpr int kX2Skip = 4, kX2Done = 5;                 // record classes beside TileClass: slot past the last tile / no more tiles
 
 __host__ __device__ inline Reach tile_reach_ext(const double *A, int ex, int ey, int ez)
 {
@@ -306,7 +310,8 @@ struct X2Smem {
     static constexpr unsigned kStageBytes = (kBoxBytes + 127u) & ~127u;
     static constexpr unsigned kBarOff = kStageBytes * NST;                 // full[NST], empty[NST], info_full[2], info_empty[2]
     static constexpr unsigned kInfoOff = kBarOff + 16u * NST + 32u;
-    static constexpr unsigned kBytes = kInfoOff + (unsigned)sizeof(TileInfo) * 64u;
+    static constexpr unsigned kCoordOff = (kInfoOff + (unsigned)sizeof(TileInfo) * 2u * kX2Pass + 15u) & ~15u;   // int4 (i0, j0, k0, -) per record
+    static constexpr unsigned kBytes = kCoordOff + 16u * 2u * kX2Pass;
 };
 
 // Resample-only kernel (Rigid.create_image / sitk.Resample): grid.x persistent CTAs stride over the 64 x 8 x 8 tiles.  Warps 0..7: consumers (warp =
@@ -327,7 +332,7 @@ tile_x2_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
 #pragma unroll
         for (int q = 0; q < 12; ++q) A[q] = Ap[q];
     }
-    // Tile records travel in passes of 32 (two passes resident) behind their own barrier pair, because only tiles that
+    // Tile records travel in passes of kX2Pass (two passes resident) behind their own barrier pair, because only tiles that
     // need a box take a ring slot: a tile outside the volume (18.6 % of config 2's tiles, the auto-crop corners) or one
     // too large for the box costs the ring nothing, so the box of the tile AFTER it is requested as soon as a slot is
     // free instead of one (very short) tile ahead (206 -> 203 us on config 2).
@@ -351,49 +356,54 @@ tile_x2_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
     }
     __syncthreads();
 
+    // Tiles are handed out in chunks of kX2Pass consecutive tiles (one pass of records).  With a claim counter
+    // (p.ws_ticket: {next tile, CTAs that are done}) a CTA takes the next chunk whenever its producer has room for one,
+    // so a CTA that drew cheap tiles (background corners) simply takes more of them; without one the chunks go round-robin.
+    // Static round-robin left ~11 % of the SM time idle at the end of config 2 (90 tiles per CTA of cost 0.1 .. 1.4:
+    // the slowest of 296 sums sets the time), and far more on a z-slab of it (11 tiles per CTA on 8 GPUs).
     const int txy = p.ntx * p.nty;
-    const int step_z = (int)(gridDim.x / (unsigned)txy), step_r = (int)(gridDim.x % (unsigned)txy);
-    const int step_y = step_r / p.ntx, step_x = step_r % p.ntx;
-    int tiz = (int)(blockIdx.x / (unsigned)txy);
-    int tiy = (int)(blockIdx.x % (unsigned)txy) / p.ntx, tix = (int)(blockIdx.x % (unsigned)txy) % p.ntx;
-    const int ntile_mine = (int)((p.ntiles - 1 - blockIdx.x) / gridDim.x) + 1;
+    const unsigned ntiles = (unsigned)p.ntiles;
+    unsigned *const claim = p.ws_ticket;
+    int4 *coords = reinterpret_cast<int4 *>(xsm + L::kCoordOff);
 
     if (warp == kX2Consumers) {
         // ---------------- producer warp ----------------
         const Reach reach = tile_reach_ext(A, kXW - 1, kXH - 1, kXD - 1);
         unsigned s = 0, ph = 0;
-        for (int base = 0; base < ntile_mine; base += 32) {
-            const int n = base + lane;
+        for (int pass = 0;; ++pass) {
+            unsigned base = 0;
+            // the first chunk of every CTA is its own (no atomic round trip before the first box can be requested)
+            if (lane == 0)
+                base = (claim && pass > 0) ? gridDim.x * (unsigned)kX2Pass + atomicAdd(claim, (unsigned)kX2Pass)
+                                           : (blockIdx.x + (unsigned)pass * gridDim.x) * (unsigned)kX2Pass;
+            base = __shfl_sync(0xffffffffu, base, 0);
+            const bool done = base >= ntiles;
             TileInfo mine;
             mine.rx = mine.ry = mine.rz = 0;
             mine.bx = mine.by = mine.bz = 0;
-            mine.cls = kOutside;
-            if (n < ntile_mine) {
-                const unsigned tile = blockIdx.x + (unsigned)n * gridDim.x;
+            mine.cls = done ? kX2Done : kX2Skip;
+            int4 c = make_int4(0, 0, 0, 0);
+            if (lane < kX2Pass && base + (unsigned)lane < ntiles) {
+                const unsigned tile = base + (unsigned)lane;
                 const int z = (int)(tile / (unsigned)txy), r2 = (int)(tile % (unsigned)txy);
-                mine = x2_classify<BOX>(A, reach, (r2 % p.ntx) * kXW, (r2 / p.ntx) * kXH, z * kXD, p.mov.nx, p.mov.ny, p.mov.nz);
+                c = make_int4((r2 % p.ntx) * kXW, (r2 / p.ntx) * kXH, z * kXD, 0);
+                mine = x2_classify<BOX>(A, reach, c.x, c.y, c.z, p.mov.nx, p.mov.ny, p.mov.nz);
             }
-            const int pass = base >> 5;
             if (pass >= 2 && lane == 0) mbar_wait<200>(ibar + 16 + 8 * (pass & 1), (unsigned)(((pass - 2) >> 1) & 1));
             __syncwarp();                                   // the consumers are done with the records of pass - 2
-            infos[(base & 32) + lane] = mine;
+            if (lane < kX2Pass) {
+                infos[(pass & 1) * kX2Pass + lane] = mine;
+                coords[(pass & 1) * kX2Pass + lane] = c;
+            }
             __syncwarp();
             if (lane == 0) mbar_arrive(ibar + 8 * (pass & 1));
-            const int cnt_pass = min(32, ntile_mine - base);
-            for (int q = 0; q < cnt_pass; ++q) {
+            if (done) break;
+#pragma unroll 1
+            for (int q = 0; q < kX2Pass; ++q) {
                 const int cls = __shfl_sync(0xffffffffu, mine.cls, q);
                 const int bx = __shfl_sync(0xffffffffu, mine.bx, q);
                 const int by = __shfl_sync(0xffffffffu, mine.by, q);
                 const int bz = __shfl_sync(0xffffffffu, mine.bz, q);
-#if MIA_X2_PREFETCH > 0
-                {   // pull the box of a later tile of this pass into L2 while the ring is full
-                    const int qn = min(q + MIA_X2_PREFETCH, 31);
-                    const int pc = __shfl_sync(0xffffffffu, mine.cls, qn), px = __shfl_sync(0xffffffffu, mine.bx, qn);
-                    const int py = __shfl_sync(0xffffffffu, mine.by, qn), pz = __shfl_sync(0xffffffffu, mine.bz, qn);
-                    if (lane == 0 && q + MIA_X2_PREFETCH < cnt_pass && (pc == kInterior || pc == kBorder))
-                        asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(&tmap), "r"(px), "r"(py), "r"(pz) : "memory");
-                }
-#endif
                 if (cls != kInterior && cls != kBorder) continue;          // no box, no ring slot
                 if (lane == 0) {
                     mbar_wait<200>(bar0 + 8 * (NST + s), ph ^ 1u);
@@ -404,20 +414,26 @@ tile_x2_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
             }
             __syncwarp();
         }
+        // This CTA claims nothing more.  The last CTA to say so puts the counter pair back to zero for the next launch
+        // that is handed this slot (no CTA touches `next` after its own increment of `done`).
+        if (claim && lane == 0) {
+            __threadfence();
+            if (atomicAdd(claim + 1, 1u) == gridDim.x - 1) {
+                claim[0] = 0u;
+                claim[1] = 0u;
+            }
+        }
     } else {
         // ---------------- consumers: 8 warps ----------------
         const X2Geom geom = x2_make_geom(A, lane, warp);
         unsigned s = 0, ph = 0;
-        for (int n = 0; n < ntile_mine; ++n) {
-            const int i0 = tix * kXW, j0 = tiy * kXH, k0 = tiz * kXD;
-            tix += step_x;
-            if (tix >= p.ntx) { tix -= p.ntx; ++tiy; }
-            tiy += step_y;
-            if (tiy >= p.nty) { tiy -= p.nty; ++tiz; }
-            tiz += step_z;
-            const int pass = n >> 5;
-            if ((n & 31) == 0) mbar_wait<32>(ibar + 8 * (pass & 1), (unsigned)((pass >> 1) & 1));      // records of this pass
-            const TileInfo ti = infos[n & 63];
+        for (int n = 0;; ++n) {
+            const int pass = n / kX2Pass, q = n % kX2Pass;
+            if (q == 0) mbar_wait<32>(ibar + 8 * (pass & 1), (unsigned)((pass >> 1) & 1));      // records of this pass
+            const TileInfo ti = infos[(pass & 1) * kX2Pass + q];
+            if (ti.cls == kX2Done) break;
+            const int4 c = coords[(pass & 1) * kX2Pass + q];
+            const int i0 = c.x, j0 = c.y, k0 = c.z;
             if (ti.cls == kInterior || ti.cls == kBorder) {
                 mbar_wait<32>(bar0 + 8 * s, ph);
                 const uint32_t stage = smem_u32(xsm + L::kStageBytes * s);
@@ -431,10 +447,10 @@ tile_x2_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
                 if (++s == NST) { s = 0; ph ^= 1u; }
             } else if (ti.cls == kOutside) {
                 x2_fill_background<VTK>(p, i0, j0, k0, lane, warp);
-            } else {
+            } else if (ti.cls == kNoFit) {
                 x2_tile_nobox<VTK>(p, p.dA ? p.dA : p.A0.a, i0, j0, k0, lane, warp);
-            }
-            if ((n & 31) == 31 || n == ntile_mine - 1) {
+            }                                               // kX2Skip: past the last tile, nothing to do
+            if (q == kX2Pass - 1) {
                 __syncwarp();
                 if (lane == 0) mbar_arrive(ibar + 16 + 8 * (pass & 1));
             }

@@ -47,6 +47,23 @@ def main():
     r["gvoxel_s"] = dims[0] * dims[1] * dims[2] / r["us_med"] / 1e3
     r["frac"] = (2.0 * mov_h.size + 2.0 * dims[0] * dims[1] * dims[2]) / (r["us_med"] * 1e-6) / 1e9 / bench.measured_peak()[0]
     out["c2_store_vtk"] = r
+    # one eighth of the lattice (the z-slab one of 8 GPUs computes): 11 tiles per CTA, where the tile order matters most
+    nz8 = (dims[2] + 7) // 8 // 8 * 8
+    k0 = 3 * nz8
+    A8 = np.array(A, dtype=np.float64).reshape(3, 4).copy()
+    A8[:, 3] += A8[:, 2] * k0
+    o8 = [torch.empty((nz8, dims[1], dims[0]), dtype=torch.int16, device=dev) for _ in range(3)]
+
+    def c2_slab():
+        i = st["i"] = (st["i"] + 1) % 3
+        kernels.resample(movs[i], A8, (nz8, dims[1], dims[0]), background=-3001.0, mode="vtk", out=o8[i])
+    r = timeit(c2_slab)
+    r["path"] = int(lib.mia_debug_last_path())
+    r["identical_to_whole"] = bool(torch.equal(o8[0], outs[0][k0:k0 + nz8]))
+    out["c2_slab_of_8"] = r
+    if os.environ.get("K2_DEV_ONLY_C2"):
+        print(json.dumps(out))
+        return
     # ITK mode onto the fixed lattice (C4 flavour) with SSD + store, and SSD evaluate
     g1 = G.Grid((512, 512, 300), bench.SPACING, tuple(-0.5 * np.array(bench.SPACING) * np.array(bench.SHAPE[::-1])))
     M = G.params_to_matrix(bench.GT, (0.0, 0.0, 0.0))

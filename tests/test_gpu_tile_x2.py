@@ -180,3 +180,65 @@ def test_multi_x2_gate_hands_large_rotations_to_the_32_wide_kernel(cuda_device):
     assert torch.equal(cd, ch) and float(((sd - sh).abs() / sh).max()) <= 1e-6
     want, n = native.reslice_ssd(fixed, moving, A[0], "itk")
     assert abs(int(cd[0]) - n) <= 2 and abs(float(sd[0]) - want) <= 1e-5 * want
+
+
+def _autocrop_case(shape=(60, 136, 264), sp=(0.9765625, 0.9765625, 2.5), seed=11):
+    """A lattice with outside, border and interior tiles (what makes the tile costs uneven)."""
+    mov = make_phantom(shape, "CT", seed=seed, spacing=sp)
+    g = grid_of(shape, sp)
+    M = G.params_to_matrix([3, -2, 4, 5, -3, 7], (0, 0, 0))
+    origin, dims = G.autocrop_extent(g, M, sp, convention="vtk")
+    A = G.compose_index_matrix(G.Grid(dims, sp, origin), g, M, convention="vtk")
+    return mov, A, (dims[2], dims[1], dims[0])
+
+
+def test_x2_claimed_tile_order_writes_the_bytes_of_the_static_order(cuda_device):
+    """Tiles are claimed from a per-launch counter (mia_b200.cu::x2_claim_slot).  Which CTA computes a tile changes no
+    bit of it, a launch leaves its counter pair at zero for the next one, launches on two streams own different pairs,
+    and a captured launch keeps its pair over the replays of its graph."""
+    lib = _lib.load()
+    mov, A, oshape = _autocrop_case()
+    t = torch.from_numpy(mov).to(cuda_device)
+    prev = lib.mia_debug_x2_static(1)
+    try:
+        want = kernels.resample(t, A, oshape, background=BG["vtk"], mode="vtk")
+        assert last_path() == X2
+        assert lib.mia_debug_x2_static(0) == 1
+        for _ in range(6):                                   # counters come back to zero: every launch writes every voxel
+            got = torch.full(oshape, 777, dtype=torch.int16, device=cuda_device)
+            kernels.resample(t, A, oshape, background=BG["vtk"], mode="vtk", out=got)
+            assert last_path() == X2 and torch.equal(got, want)
+        # two streams at once
+        s1, s2 = torch.cuda.Stream(cuda_device), torch.cuda.Stream(cuda_device)
+        outs = [torch.full(oshape, 777, dtype=torch.int16, device=cuda_device) for _ in range(8)]
+        torch.cuda.synchronize()
+        for i, o in enumerate(outs):
+            with torch.cuda.stream(s1 if i % 2 == 0 else s2):
+                kernels.resample(t, A, oshape, background=BG["vtk"], mode="vtk", out=o)
+        torch.cuda.synchronize()
+        assert all(torch.equal(o, want) for o in outs)
+        # captured once, replayed three times, with eager launches in between
+        o_g = torch.full(oshape, 777, dtype=torch.int16, device=cuda_device)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            kernels.resample(t, A, oshape, background=BG["vtk"], mode="vtk", out=o_g)
+            kernels.resample(t, A, oshape, background=BG["vtk"], mode="vtk", out=outs[0])
+        for _ in range(3):
+            o_g.fill_(777); outs[0].fill_(777)
+            graph.replay()
+            kernels.resample(t, A, oshape, background=BG["vtk"], mode="vtk", out=outs[1])
+            torch.cuda.synchronize()
+            assert torch.equal(o_g, want) and torch.equal(outs[0], want) and torch.equal(outs[1], want)
+    finally:
+        lib.mia_debug_x2_static(prev)
+
+
+def test_x2_fewer_chunks_than_ctas(cuda_device):
+    """A lattice of a few tiles: the grid shrinks to the number of chunks, and chunks past the last tile hold skip records."""
+    shape, sp = (9, 17, 72), (1.0, 1.0, 2.0)
+    mov = make_phantom(shape, "CT", seed=3, spacing=sp)
+    g = grid_of(shape, sp)
+    A = G.compose_index_matrix(g, g, G.params_to_matrix([0.5, -0.5, 1, 2, -1, 1], (0, 0, 0)))
+    for od in ((72, 17, 9), (65, 9, 8), (130, 8, 17), (64, 8, 8), (1, 1, 1)):
+        run(cuda_device, mov, A, od, "vtk")
+        run(cuda_device, mov, A, od, "itk")
