@@ -728,6 +728,26 @@ def main():
         e2e_info = {"api": "mia_resample_rigid_host (pinned host in/out, H2D+kernel+D2H pipelined by z-slab)",
                     "h2d_bytes_per_step": 2 * mov_h.size, "d2h_bytes_per_step": 2 * nvox_out,
                     "max_abs_diff_vs_device_path": int(np.abs(pin_out.astype(np.int32) - outs[(K - 1) % ring].cpu().numpy().astype(np.int32)).max())}
+        # What the link alone allows: the same bytes as bare copies, both directions at once, no kernel (the pipeline can
+        # at best hide everything else behind the longer of the two)
+        pin_floor = kernels.pinned_empty(oshape, np.int16)      # not pin_out: its bytes are compared with the device path below
+        t_in, t_out = torch.from_numpy(pin_in), torch.from_numpy(pin_floor)
+        d_in = torch.empty(SHAPE, dtype=torch.int16, device=dev)
+        s_up, s_down = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        floor = []
+        for _ in range(4):
+            torch.cuda.synchronize(dev)
+            t0 = time.perf_counter()
+            with torch.cuda.stream(s_up):
+                d_in.copy_(t_in, non_blocking=True)
+            with torch.cuda.stream(s_down):
+                t_out.copy_(outs[(K - 1) % ring], non_blocking=True)
+            torch.cuda.synchronize(dev)
+            floor.append(time.perf_counter() - t0)
+        del d_in, t_out, pin_floor
+        e2e_info["link_floor_ms"] = 1e3 * min(floor[1:])
+        e2e_info["link_floor_note"] = ("bare pinned H2D of the input and D2H of the output, concurrently, best of 3: the "
+                                       "time the host link alone needs for one step")
         host_out = pin_out
     else:
         # ONE host volume in a shared mapping; each rank pins and moves only its own planes of it

@@ -50,7 +50,7 @@ const char *mia_last_error(void);
 /* Diagnostic: which kernel the calling thread's last resample / metric call launched
  * (0 = direct per-voxel kernel, 1 = TMA-staged 32-wide tile kernel, 2 = multi-matrix tile kernel, 3 = DVF tile kernel,
  * 4 / 7 / 8 = the tile kernel with the tall / deep / cube box family, 5 = x-pair tile kernel, 6 = x-pair multi-matrix
- * kernel).  Used by the parity tests. */
+ * kernel, 9 = software-pipelined DVF tile kernel).  Used by the parity tests. */
 int mia_debug_last_path(void);
 /* Diagnostic / escape hatch: the x-pair kernel hands its tiles out through a per-launch claim counter (CTAs that drew
  * cheap tiles take more of them).  on != 0 keeps the static round-robin order instead (the same voxels either way,

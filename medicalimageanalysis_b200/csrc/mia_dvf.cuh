@@ -55,6 +55,13 @@ constexpr int kDvfThreads = 256;
 #ifndef MIA_DVF_MINB
 #define MIA_DVF_MINB 4
 #endif
+// min / max that PROPAGATE NaN (fminf / fmaxf drop it): a NaN displacement must poison the column's coordinate range so
+// that the column fails the "strictly interior" test and takes the per-voxel branch, where NaN compares as outside.
+__device__ __forceinline__ float min_nan(float a, float b) { float r; asm("min.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ float max_nan(float a, float b) { float r; asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ float min3_nan(float a, float b, float c) { float r; asm("min.NaN.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }   // FMNMX3
+__device__ __forceinline__ float max3_nan(float a, float b, float c) { float r; asm("max.NaN.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
+
 constexpr int kDvfTZ = MIA_DVF_TZ;   // planes per thread: the float64 part of the coordinate is paid once per kDvfTZ voxels
 
 // Work item = 32 (x) x 8 (y) x 8 (z) output voxels per CTA pass: lane = x (coalesced field reads and stores),
@@ -230,12 +237,12 @@ warp_dvf_tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
                     ly[kz] = ry + fmaf(b12, d[kz][2], fmaf(b11, d[kz][1], b10 * d[kz][0]));
                     lz[kz] = rz + fmaf(b22, d[kz][2], fmaf(b21, d[kz][1], b20 * d[kz][0]));
                 }
-                fmnx = fminf(fmnx, lx[kz]); fmxx = fmaxf(fmxx, lx[kz]);
-                fmny = fminf(fmny, ly[kz]); fmxy = fmaxf(fmxy, ly[kz]);
-                fmnz = fminf(fmnz, lz[kz]); fmxz = fmaxf(fmxz, lz[kz]);
+                fmnx = min_nan(fmnx, lx[kz]); fmxx = max_nan(fmxx, lx[kz]);
+                fmny = min_nan(fmny, ly[kz]); fmxy = max_nan(fmxy, ly[kz]);
+                fmnz = min_nan(fmnz, lz[kz]); fmxz = max_nan(fmxz, lz[kz]);
             }
         }
-        // NaN coordinates fail the comparisons below and take the per-voxel path, where they are outside
+        // NaN coordinates (kept by min_nan / max_nan) fail the comparisons below and take the per-voxel path, where they are outside
         const bool interior = (kcnt == kTZ) & (fmnx >= clox) & (fmxx <= chix) & (fmny >= cloy) & (fmxy <= chiy) &
                               (fmnz >= cloz) & (fmxz <= chiz);
         if (interior) {
@@ -339,6 +346,339 @@ warp_dvf_tile_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
             }
         }
         __syncthreads();          // the box and s_box are free again
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Software-pipelined form of the box-staged warp: BOTH round trips of a tile (field, box) overlap arithmetic.
+//   iteration for tile t:   [coordinates + bounding box of tile t+1, from its field buffer]     <- box(t) in flight
+//                           [wait box(t); interpolate tile t; store]
+//                           __syncthreads
+//                           [one thread: request box(t+1) and the field of tile t+2 + ...]
+// The coordinates of tile t+1 stay in registers while tile t is interpolated (24 floats more than the serial kernel),
+// so this kernel runs TWO CTAs of up to 128 registers per SM instead of three of 80, with the field double-buffered
+// (box + 2 x 24 KB).  One CTA barrier per tile instead of two.
+constexpr unsigned kDvfFieldBytes = 96u * 8u * 8u * 4u;     // one tile of the field: 32 x 8 x 8 vectors of 3 floats
+
+struct DvfTile {                 // what the coordinate phase leaves for the interpolation phase, per thread
+    float lx[kTZ], ly[kTZ], lz[kTZ];      // local coordinates relative to (bx, by, bz), clamped on border columns
+    unsigned inbits;                      // voxel kz is inside the moving volume
+    int bx, by, bz;                       // thread base: floor of the rigid coordinate of the first voxel
+    int kcnt;                             // planes of this column that exist (0: column outside the lattice)
+    unsigned v;                           // output offset of the first voxel (< 2^31: checked by the host)
+};
+
+struct DvfConsts { float a2x, a2y, a2z, b[9]; };       // float32 images of A's z column and of B, formed once per thread
+
+struct DvfWalk {                 // tile coordinates of the tiles t0, t0 + g, t0 + 2 g, ... without a division per tile
+    int tix, tiy, tiz, step_x, step_y, step_z, ntx, nty;
+    __device__ __forceinline__ void init(unsigned t0, unsigned g, int ntx_, int nty_)
+    {
+        ntx = ntx_; nty = nty_;
+        const unsigned txy = (unsigned)(ntx * nty);
+        tiz = (int)(t0 / txy); tiy = (int)(t0 % txy) / ntx; tix = (int)(t0 % txy) % ntx;
+        step_z = (int)(g / txy); step_y = (int)(g % txy) / ntx; step_x = (int)(g % txy) % ntx;
+    }
+    __device__ __forceinline__ void advance()
+    {
+        tix += step_x;
+        if (tix >= ntx) { tix -= ntx; ++tiy; }
+        tiy += step_y;
+        if (tiy >= nty) { tiy -= nty; ++tiz; }
+        tiz += step_z;
+    }
+};
+
+template <bool CLOSED, bool DIAG>
+__device__ __forceinline__ void dvf_coords(const DvfParams &p, const DvfConsts &c, const float *fbuf, const DvfWalk &w, int lane,
+                                           int warp, DvfTile &st, int (*sbox)[6])
+{
+    const double *A = p.A.a;
+    const int nx = p.mov.nx, ny = p.mov.ny, nz = p.mov.nz;
+    const int i = w.tix * 32 + lane, j = w.tiy * 8 + warp, k0 = w.tiz * kTZ;
+    const bool row_ok = (i < p.ox) & (j < p.oy);
+    st.kcnt = row_ok ? min(kTZ, p.oz - k0) : 0;
+    const double cx = ((A[3] + (double)k0 * A[2]) + (double)j * A[1]) + (double)i * A[0];
+    const double cy = ((A[7] + (double)k0 * A[6]) + (double)j * A[5]) + (double)i * A[4];
+    const double cz = ((A[11] + (double)k0 * A[10]) + (double)j * A[9]) + (double)i * A[8];
+    const RowCtx r = make_point_ctx(cx, cy, cz, nx, ny, nz);
+    st.bx = r.bx; st.by = r.by; st.bz = r.bz;
+    st.v = ((unsigned)k0 * (unsigned)p.oy + (unsigned)j) * (unsigned)p.ox + (unsigned)i;
+    const float hix = CLOSED ? r.hix : prev_float(r.hix), hiy = CLOSED ? r.hiy : prev_float(r.hiy), hiz = CLOSED ? r.hiz : prev_float(r.hiz);
+    const float clox = -(float)r.bx, cloy = -(float)r.by, cloz = -(float)r.bz;
+    const float chix = (float)(nx - 1) - (float)r.bx, chiy = (float)(ny - 1) - (float)r.by, chiz = (float)(nz - 1) - (float)r.bz;
+    float fmnx = INFINITY, fmny = INFINITY, fmnz = INFINITY, fmxx = -INFINITY, fmxy = -INFINITY, fmxz = -INFINITY;
+    const float *q = fbuf + warp * 96 + 3 * lane;
+    // two planes per step: packed FFMA2 for the coordinates, one 3-input FMNMX per range end (NaN kept, see min_nan)
+    const f32x2 ax2 = pk(c.a2x, c.a2x), ay2 = pk(c.a2y, c.a2y), az2 = pk(c.a2z, c.a2z);
+    const f32x2 fx2 = pk(r.fx, r.fx), fy2 = pk(r.fy, r.fy), fz2 = pk(r.fz, r.fz);
+#pragma unroll
+    for (int kz = 0; kz < kTZ; kz += 2) {
+        const f32x2 d0 = pk(q[kz * 768], q[kz * 768 + 768]), d1 = pk(q[kz * 768 + 1], q[kz * 768 + 769]),
+                    d2 = pk(q[kz * 768 + 2], q[kz * 768 + 770]);                           // zero past the field's edge
+        const f32x2 kk = pk((float)kz, (float)(kz + 1));
+        const f32x2 rx = fma2(kk, ax2, fx2), ry = fma2(kk, ay2, fy2), rz = fma2(kk, az2, fz2);
+        f32x2 x2, y2, z2;
+        if (DIAG) {
+            x2 = fma2(pk(c.b[0], c.b[0]), d0, rx);
+            y2 = fma2(pk(c.b[4], c.b[4]), d1, ry);
+            z2 = fma2(pk(c.b[8], c.b[8]), d2, rz);
+        } else {
+            x2 = add2(rx, fma2(pk(c.b[2], c.b[2]), d2, fma2(pk(c.b[1], c.b[1]), d1, mul2(pk(c.b[0], c.b[0]), d0))));
+            y2 = add2(ry, fma2(pk(c.b[5], c.b[5]), d2, fma2(pk(c.b[4], c.b[4]), d1, mul2(pk(c.b[3], c.b[3]), d0))));
+            z2 = add2(rz, fma2(pk(c.b[8], c.b[8]), d2, fma2(pk(c.b[7], c.b[7]), d1, mul2(pk(c.b[6], c.b[6]), d0))));
+        }
+        upk(x2, st.lx[kz], st.lx[kz + 1]);
+        upk(y2, st.ly[kz], st.ly[kz + 1]);
+        upk(z2, st.lz[kz], st.lz[kz + 1]);
+        fmnx = min3_nan(fmnx, st.lx[kz], st.lx[kz + 1]); fmxx = max3_nan(fmxx, st.lx[kz], st.lx[kz + 1]);
+        fmny = min3_nan(fmny, st.ly[kz], st.ly[kz + 1]); fmxy = max3_nan(fmxy, st.ly[kz], st.ly[kz + 1]);
+        fmnz = min3_nan(fmnz, st.lz[kz], st.lz[kz + 1]); fmxz = max3_nan(fmxz, st.lz[kz], st.lz[kz + 1]);
+    }
+    // strictly interior columns need no test and no clamp (a NaN range fails the comparisons)
+    const bool interior = (st.kcnt == kTZ) & (fmnx >= clox) & (fmxx <= chix) & (fmny >= cloy) & (fmxy <= chiy) &
+                          (fmnz >= cloz) & (fmxz <= chiz);
+    if (interior) {
+        st.inbits = 0xffu;
+    } else {
+        st.inbits = 0u;
+        fmnx = fmny = fmnz = INFINITY;
+        fmxx = fmxy = fmxz = -INFINITY;
+#pragma unroll
+        for (int kz = 0; kz < kTZ; ++kz) {
+            float x = st.lx[kz], y = st.ly[kz], z = st.lz[kz];
+            const bool in = (kz < st.kcnt) & (x >= r.lox) & (x <= hix) & (y >= r.loy) & (y <= hiy) & (z >= r.loz) & (z <= hiz);
+            x = fminf(fmaxf(x, clox), chix); y = fminf(fmaxf(y, cloy), chiy); z = fminf(fmaxf(z, cloz), chiz);
+            st.lx[kz] = x; st.ly[kz] = y; st.lz[kz] = z;
+            if (in) {
+                st.inbits |= 1u << kz;
+                fmnx = fminf(fmnx, x); fmxx = fmaxf(fmxx, x);
+                fmny = fminf(fmny, y); fmxy = fmaxf(fmxy, y);
+                fmnz = fminf(fmnz, z); fmxz = fmaxf(fmxz, z);
+            }
+        }
+    }
+    const int mnx = (int)floorf(fmnx), mxx = (int)floorf(fmxx), mny = (int)floorf(fmny), mxy = (int)floorf(fmxy),
+              mnz = (int)floorf(fmnz), mxz = (int)floorf(fmxz);           // garbage when inbits == 0: not used then
+    const bool any = st.inbits != 0u;
+    const int big = 0x7fffffff;
+    const int wmnx = __reduce_min_sync(0xffffffffu, any ? r.bx + mnx : big), wmxx = __reduce_max_sync(0xffffffffu, any ? r.bx + mxx : -big);
+    const int wmny = __reduce_min_sync(0xffffffffu, any ? r.by + mny : big), wmxy = __reduce_max_sync(0xffffffffu, any ? r.by + mxy : -big);
+    const int wmnz = __reduce_min_sync(0xffffffffu, any ? r.bz + mnz : big), wmxz = __reduce_max_sync(0xffffffffu, any ? r.bz + mxz : -big);
+    if (lane == 0) {
+        sbox[warp][0] = wmnx; sbox[warp][1] = wmxx; sbox[warp][2] = wmny;
+        sbox[warp][3] = wmxy; sbox[warp][4] = wmnz; sbox[warp][5] = wmxz;
+    }
+}
+
+struct DvfBoxPlace { int bx0, by0, bz0; bool none, fits; };
+
+template <typename TM, class BOX>
+__device__ __forceinline__ DvfBoxPlace dvf_place(const int (*sbox)[6])
+{
+    constexpr int xalign = 16 / (int)sizeof(TM);
+    const int big = 0x7fffffff;
+    int bx0 = big, bx1 = -big, by0 = big, by1 = -big, bz0 = big, bz1 = -big;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+        bx0 = min(bx0, sbox[w][0]); bx1 = max(bx1, sbox[w][1]);
+        by0 = min(by0, sbox[w][2]); by1 = max(by1, sbox[w][3]);
+        bz0 = min(bz0, sbox[w][4]); bz1 = max(bz1, sbox[w][5]);
+    }
+    DvfBoxPlace b;
+    b.none = bx0 == big;
+    bx0 &= ~(xalign - 1);                                   // TMA: inner coordinate * element size = 0 mod 16 bytes
+    b.fits = !b.none && (bx1 + 2 - bx0 <= BOX::kX) && (by1 + 2 - by0 <= BOX::kY) && (bz1 + 2 - bz0 <= BOX::kZ);
+    b.bx0 = bx0; b.by0 = by0; b.bz0 = bz0;
+    return b;
+}
+
+template <typename TM, typename TO, bool CLOSED, class BOX>
+__device__ __forceinline__ void dvf_interp(const DvfParams &p, const DvfTile &st, const DvfBoxPlace &b, uint32_t box_smem,
+                                           uint32_t bar, unsigned &phase)
+{
+    constexpr unsigned ES = sizeof(TM);
+    constexpr int PY = BOX::kX * ES, PZ = BOX::kX * BOX::kY * ES;
+    const unsigned plane = (unsigned)p.oy * (unsigned)p.ox;
+    const TO bg = tile_to_out<TO, CLOSED>(p.background);
+    TO *o = static_cast<TO *>(p.out) + st.v;
+    const f32x2 magic2 = pk(kMagic, kMagic);
+    if (b.none) {
+#pragma unroll
+        for (int kz = 0; kz < kTZ; ++kz)
+            if (kz < st.kcnt) st_out(o + (size_t)kz * plane, bg);
+    } else if (!b.fits) {
+        // a tear in the field: per-voxel gather (coordinates were clamped; weights beyond the edge are 0)
+        RowCtx r;
+        r.bx = st.bx; r.by = st.by; r.bz = st.bz;
+        r.fx = r.fy = r.fz = 0.0f; r.ax = r.ay = r.az = 0.0f;
+        r.lox = -0.5f - (float)r.bx; r.loy = -0.5f - (float)r.by; r.loz = -0.5f - (float)r.bz;
+        r.hix = (float)p.mov.nx - 0.5f - (float)r.bx; r.hiy = (float)p.mov.ny - 0.5f - (float)r.by; r.hiz = (float)p.mov.nz - 0.5f - (float)r.bz;
+        const TM *__restrict__ mov = static_cast<const TM *>(p.mov.p);
+#pragma unroll
+        for (int kz = 0; kz < kTZ; ++kz) {
+            if (kz < st.kcnt) {
+                float val = 0.0f;
+                const bool in = (st.inbits >> kz) & 1u;
+                if (in) sample_local<TM, true>(mov, p.mov.nx, p.mov.ny, p.mov.nz, r, st.lx[kz], st.ly[kz], st.lz[kz], val);
+                st_out(o + (size_t)kz * plane, in ? tile_to_out<TO, CLOSED>(val) : bg);
+            }
+        }
+    } else {
+        const int tbx = st.bx - b.bx0, tby = st.by - b.by0, tbz = st.bz - b.bz0;
+        const uint32_t ubase = box_smem + (uint32_t)((tbz * BOX::kY + tby) * BOX::kX + tbx) * ES + p.magic_fold;
+        // a voxel that is outside contributed nothing to the box: its (unused) taps are taken at box element (0, 0, 0)
+        const float sx = (float)(-tbx), sy = (float)(-tby), sz = (float)(-tbz);
+        mbar_wait<64>(bar, phase);
+        phase ^= 1u;
+#pragma unroll
+        for (int kp = 0; kp < kTZ; kp += 2) {
+            const bool i0 = (st.inbits >> kp) & 1u, i1 = (st.inbits >> (kp + 1)) & 1u;
+            const f32x2 lx2 = pk(i0 ? st.lx[kp] : sx, i1 ? st.lx[kp + 1] : sx), ly2 = pk(i0 ? st.ly[kp] : sy, i1 ? st.ly[kp + 1] : sy),
+                        lz2 = pk(i0 ? st.lz[kp] : sz, i1 ? st.lz[kp + 1] : sz);
+            const f32x2 tx2 = add2_rm(lx2, magic2), ty2 = add2_rm(ly2, magic2), tz2 = add2_rm(lz2, magic2);
+            const f32x2 wx2 = sub2(lx2, sub2(tx2, magic2)), wy2 = sub2(ly2, sub2(ty2, magic2)), wz2 = sub2(lz2, sub2(tz2, magic2));
+            const uint32_t a0 = mad_u32(mad_u32(mad_u32((uint32_t)tz2, BOX::kY, (uint32_t)ty2), BOX::kX, (uint32_t)tx2), ES, ubase);
+            const uint32_t a1 = mad_u32(mad_u32(mad_u32((uint32_t)(tz2 >> 32), BOX::kY, (uint32_t)(ty2 >> 32)), BOX::kX, (uint32_t)(tx2 >> 32)), ES, ubase);
+            const f32x2 v000 = pk(Tap<TM, 0>::ld(a0), Tap<TM, 0>::ld(a1));
+            const f32x2 v100 = pk(Tap<TM, ES>::ld(a0), Tap<TM, ES>::ld(a1));
+            const f32x2 v010 = pk(Tap<TM, PY>::ld(a0), Tap<TM, PY>::ld(a1));
+            const f32x2 v110 = pk(Tap<TM, PY + ES>::ld(a0), Tap<TM, PY + ES>::ld(a1));
+            const f32x2 v001 = pk(Tap<TM, PZ>::ld(a0), Tap<TM, PZ>::ld(a1));
+            const f32x2 v101 = pk(Tap<TM, PZ + ES>::ld(a0), Tap<TM, PZ + ES>::ld(a1));
+            const f32x2 v011 = pk(Tap<TM, PZ + PY>::ld(a0), Tap<TM, PZ + PY>::ld(a1));
+            const f32x2 v111 = pk(Tap<TM, PZ + PY + ES>::ld(a0), Tap<TM, PZ + PY + ES>::ld(a1));
+            const f32x2 vx00 = lerp2(wx2, v000, v100), vx10 = lerp2(wx2, v010, v110);
+            const f32x2 vx01 = lerp2(wx2, v001, v101), vx11 = lerp2(wx2, v011, v111);
+            const f32x2 vxx0 = lerp2(wy2, vx00, vx10), vxx1 = lerp2(wy2, vx01, vx11);
+            float val0, val1;
+            upk(lerp2(wz2, vxx0, vxx1), val0, val1);
+            const TO o0 = tile_to_out<TO, CLOSED>(val0), o1 = tile_to_out<TO, CLOSED>(val1);
+            if (kp < st.kcnt) st_out(o, i0 ? o0 : bg);
+            o += plane;
+            if (kp + 1 < st.kcnt) st_out(o, i1 ? o1 : bg);
+            o += plane;
+        }
+    }
+}
+
+#ifndef MIA_DVF_PIPE_MINB
+#define MIA_DVF_PIPE_MINB 2
+#endif
+template <class BOX, typename TM, int NBOX>
+struct DvfPipeSmem {
+    static constexpr unsigned kBoxBytes = BOX::kX * BOX::kY * BOX::kZ * (unsigned)sizeof(TM);
+    static constexpr unsigned kBoxStage = (kBoxBytes + 127u) & ~127u;
+    static constexpr unsigned kFieldOff = kBoxStage * NBOX;
+    static constexpr unsigned kBytes = kFieldOff + 2u * kDvfFieldBytes;
+};
+
+// NBOX = 2 (int16: two 80 x 15 x 13 boxes fit beside the field buffers of two CTAs): the box of tile t+1 is requested as
+// soon as its coordinates are reduced, BEFORE tile t is interpolated, into the other box buffer -- it has the whole
+// interpolation of tile t and the coordinate phase of tile t+2 to arrive, and the barrier after the interpolation goes.
+// NBOX = 1 (float32: 46 KB boxes): box(t+1) is requested after tile t has been interpolated and arrives during the
+// coordinate phase of tile t+2.
+template <typename TM, typename TO, bool CLOSED, class BOX, bool DIAG, int NBOX>
+__global__ void __launch_bounds__(kDvfThreads, MIA_DVF_PIPE_MINB)
+warp_dvf_pipe_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap fmap,
+                     const __grid_constant__ DvfParams p)
+{
+    using L = DvfPipeSmem<BOX, TM, NBOX>;
+    extern __shared__ __align__(1024) unsigned char dsm[];
+    __shared__ int s_box[2][8][6];
+    __shared__ __align__(8) unsigned long long s_bar[2], s_fbar[2];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ntx = (p.ox + 31) / 32, nty = (p.oy + 7) / 8, ntz = (p.oz + kTZ - 1) / kTZ;
+    const unsigned ntiles = (unsigned)ntx * nty * ntz;
+    const uint32_t box_smem = smem_u32(dsm);
+    const float *fbuf0 = reinterpret_cast<const float *>(dsm + L::kFieldOff);
+    auto request_field = [&](unsigned tt, unsigned b) {       // one thread
+        const int tz = (int)(tt / (unsigned)(ntx * nty)), r2 = (int)(tt % (unsigned)(ntx * nty));
+        const uint32_t fb = smem_u32(&s_fbar[b]);
+        mbar_arrive_expect_tx(fb, kDvfFieldBytes);
+        tma_load_3d(smem_u32(fbuf0) + b * kDvfFieldBytes, &fmap, fb, (r2 % ntx) * 96, (r2 / ntx) * 8, tz * kTZ);
+    };
+    auto request_box = [&](const DvfBoxPlace &b, unsigned buf) {     // one thread
+        const uint32_t bb = smem_u32(&s_bar[buf]);
+        mbar_arrive_expect_tx(bb, L::kBoxBytes);
+        tma_load_3d(box_smem + buf * L::kBoxStage, &tmap, bb, b.bx0, b.by0, b.bz0);
+    };
+    const unsigned t0 = blockIdx.x, g = gridDim.x;
+    if (threadIdx.x == 0) {
+        mbar_init(smem_u32(&s_bar[0]), 1);
+        mbar_init(smem_u32(&s_bar[1]), 1);
+        mbar_init(smem_u32(&s_fbar[0]), 1);
+        mbar_init(smem_u32(&s_fbar[1]), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        if (t0 < ntiles) request_field(t0, 0u);
+        if (t0 + g < ntiles) request_field(t0 + g, 1u);
+    }
+    __syncthreads();
+    if (t0 >= ntiles) return;
+    unsigned ph0 = 0, ph1 = 0, fph0 = 0, fph1 = 0;
+    DvfConsts c;
+    c.a2x = (float)p.A.a[2]; c.a2y = (float)p.A.a[6]; c.a2z = (float)p.A.a[10];
+#pragma unroll
+    for (int q = 0; q < 9; ++q) c.b[q] = (float)p.B[q];
+
+    // prologue: coordinates and box of the first tile
+    DvfWalk walk;
+    walk.init(t0, g, ntx, nty);
+    DvfTile tileA, tileB;
+    DvfBoxPlace placeA, placeB;
+    mbar_wait<64>(smem_u32(&s_fbar[0]), fph0);
+    fph0 ^= 1u;
+    dvf_coords<CLOSED, DIAG>(p, c, fbuf0, walk, lane, warp, tileA, s_box[0]);
+    walk.advance();
+    __syncthreads();
+    placeA = dvf_place<TM, BOX>(s_box[0]);
+    if (threadIdx.x == 0) {
+        if (placeA.fits) request_box(placeA, 0u);
+        if (t0 + 2 * g < ntiles) request_field(t0 + 2 * g, 0u);
+    }
+    unsigned t = t0;
+    // One tile: `cur` / `pc` were prepared by the previous step (field buffer and s_box slot CB, box buffer CB or 0); the
+    // step prepares `nxt` / `pn` in the other slot.  Two steps with the roles swapped make one loop iteration, so the
+    // 24 coordinates per thread are never copied between registers.
+    auto step = [&](auto cb_tag, DvfTile &cur, DvfBoxPlace &pc, DvfTile &nxt, DvfBoxPlace &pn) -> bool {
+        constexpr unsigned CB = decltype(cb_tag)::value, NB = 1u - CB;
+        constexpr unsigned BB = NBOX == 2 ? CB : 0u;          // box buffer of THIS tile
+        const bool more = t + g < ntiles;
+        if (more) {                                           // coordinates of tile t + g while box(t) is in flight
+            unsigned &fph = NB ? fph1 : fph0;
+            mbar_wait<64>(smem_u32(&s_fbar[NB]), fph);
+            fph ^= 1u;
+            dvf_coords<CLOSED, DIAG>(p, c, fbuf0 + NB * (kDvfFieldBytes / 4u), walk, lane, warp, nxt, s_box[NB]);
+            walk.advance();
+        }
+        if (NBOX == 2) {
+            // s_box[NB] complete, field buffer NB read by everyone, and box buffer NB (tile t - g) long done with
+            __syncthreads();
+            if (more) {
+                pn = dvf_place<TM, BOX>(s_box[NB]);
+                if (threadIdx.x == 0) {
+                    if (pn.fits) request_box(pn, NB);
+                    if (t + 3 * g < ntiles) request_field(t + 3 * g, NB);
+                }
+            }
+            dvf_interp<TM, TO, CLOSED, BOX>(p, cur, pc, box_smem + BB * L::kBoxStage, smem_u32(&s_bar[BB]), BB ? ph1 : ph0);
+        } else {
+            dvf_interp<TM, TO, CLOSED, BOX>(p, cur, pc, box_smem, smem_u32(&s_bar[0]), ph0);
+            __syncthreads();      // the box is free, s_box[NB] is complete, field buffer NB has been read by everyone
+            if (more) {
+                pn = dvf_place<TM, BOX>(s_box[NB]);
+                if (threadIdx.x == 0) {
+                    if (pn.fits) request_box(pn, 0u);
+                    if (t + 3 * g < ntiles) request_field(t + 3 * g, NB);
+                }
+            }
+        }
+        t += g;
+        return more;
+    };
+    for (;;) {
+        if (!step(std::integral_constant<unsigned, 0u>{}, tileA, placeA, tileB, placeB)) break;
+        if (!step(std::integral_constant<unsigned, 1u>{}, tileB, placeB, tileA, placeA)) break;
     }
 }
 

@@ -47,6 +47,72 @@ bool try_warp_dvf_staged(mia::DvfParams p, const void *d_mov, const int mdims[3]
     return true;
 }
 
+
+// Software-pipelined kernel (mia_dvf.cuh::warp_dvf_pipe_kernel): the field arrives by TMA too, through a tensor map of
+// the field seen as [oz][oy][3 ox] floats with one 96 x 8 x 8 box per tile -- needs ox % 4 == 0 (global strides in
+// multiples of 16 bytes) and a 16-byte aligned field; anything else takes the serial staged kernel below.
+using DvfPipeBoxI16 = mia::Box<80, 15, 13>;   // 31.2 KB, two of them: 40-word pitch (8 mod 32)
+using DvfPipeBoxF32 = mia::Box<64, 14, 13>;   // 46.6 KB, one
+
+bool dvf_pipe_disabled()
+{
+    static const bool off = [] { const char *e = getenv("MIA_DVF_NO_PIPE"); return e && *e && *e != '0'; }();
+    return off;
+}
+
+template <typename TM, class BOX, int NBOX, bool VTK, bool DIAG>
+bool dvf_launch_pipe(const CUtensorMap &map, const CUtensorMap &fmap, const mia::DvfParams &p, unsigned g, cudaStream_t s)
+{
+    auto k = mia::warp_dvf_pipe_kernel<TM, TM, VTK, BOX, DIAG, NBOX>;
+    constexpr size_t smem = mia::DvfPipeSmem<BOX, TM, NBOX>::kBytes;
+    static std::mutex mu;
+    static bool done[64] = {false};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return false;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!done[dev]) {             // more than 48 KB of dynamic shared memory: opt in once per instantiation and device
+            if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return false;
+            done[dev] = true;
+        }
+    }
+    k<<<g, mia::kDvfThreads, smem, s>>>(map, fmap, p);
+    return true;
+}
+
+template <typename TM, class BOX, int NBOX>
+bool try_warp_dvf_pipe(mia::DvfParams p, const void *d_mov, const int mdims[3], int mode, cudaStream_t s)
+{
+    if (dvf_staged_disabled() || dvf_pipe_disabled() || tile_path_disabled()) return false;
+    if (p.ox % 4 != 0 || ((uintptr_t)p.dvf & 15u) != 0) return false;
+    alignas(64) CUtensorMap map, fmap;
+    if (!make_tensor_map<TM, BOX>(&map, d_mov, mdims)) return false;
+    const long long ntiles = (long long)((p.ox + 31) / 32) * ((p.oy + 7) / 8) * ((p.oz + mia::kTZ - 1) / mia::kTZ);
+    if (ntiles > 0x7fffffffLL || (long long)p.ox * p.oy * p.oz >= 0x7fffffffLL) return false;      // 32-bit output offsets
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) return false;
+    const cuuint64_t gdim[3] = {(cuuint64_t)p.ox * 3u, (cuuint64_t)p.oy, (cuuint64_t)p.oz};
+    const cuuint64_t gstr[2] = {(cuuint64_t)p.ox * 12u, (cuuint64_t)p.ox * 12u * (cuuint64_t)p.oy};
+    const cuuint32_t box[3] = {96, 8, (cuuint32_t)mia::kTZ};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    if (enc(&fmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float *>(p.dvf), gdim, gstr, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return false;
+    p.magic_fold = 0u - mia::kMagicBits * (unsigned)((BOX::kY + 1) * BOX::kX + 1) * (unsigned)sizeof(TM);
+    long long gx = (long long)sm_count() * MIA_DVF_PIPE_MINB;
+    if (gx > ntiles) gx = ntiles;
+    const bool diag = (float)p.B[1] == 0.0f && (float)p.B[2] == 0.0f && (float)p.B[3] == 0.0f && (float)p.B[5] == 0.0f &&
+                      (float)p.B[6] == 0.0f && (float)p.B[7] == 0.0f;
+    const unsigned g = (unsigned)gx;
+    const bool ok = mode == MIA_MODE_VTK
+        ? (diag ? dvf_launch_pipe<TM, BOX, NBOX, true, true>(map, fmap, p, g, s) : dvf_launch_pipe<TM, BOX, NBOX, true, false>(map, fmap, p, g, s))
+        : (diag ? dvf_launch_pipe<TM, BOX, NBOX, false, true>(map, fmap, p, g, s) : dvf_launch_pipe<TM, BOX, NBOX, false, false>(map, fmap, p, g, s));
+    if (!ok) return false;
+    g_last_path = 9;
+    return true;
+}
+
 }  // namespace
 
 extern "C" {
@@ -79,8 +145,11 @@ int mia_warp_dvf(const void *d_mov, int mov_dtype, const int mdims[3], const flo
     if (gx > nwork) gx = nwork;
     cudaStream_t s = (cudaStream_t)stream;
     g_last_path = 0;
-    const bool staged = mov_dtype == MIA_I16 ? try_warp_dvf_staged<int16_t, DvfBoxI16>(p, d_mov, mdims, mode, s)
-                                             : try_warp_dvf_staged<float, DvfBoxF32>(p, d_mov, mdims, mode, s);
+    bool staged = mov_dtype == MIA_I16 ? try_warp_dvf_pipe<int16_t, DvfPipeBoxI16, 2>(p, d_mov, mdims, mode, s)
+                                       : try_warp_dvf_pipe<float, DvfPipeBoxF32, 1>(p, d_mov, mdims, mode, s);
+    if (!staged)
+        staged = mov_dtype == MIA_I16 ? try_warp_dvf_staged<int16_t, DvfBoxI16>(p, d_mov, mdims, mode, s)
+                                      : try_warp_dvf_staged<float, DvfBoxF32>(p, d_mov, mdims, mode, s);
     if (staged) {
         CUDA_TRY(cudaGetLastError());
         return MIA_OK;

@@ -12,6 +12,7 @@ from oracle import dvf as D
 from tests.test_oracle_dvf import _smooth_field
 
 pytestmark = pytest.mark.gpu
+STAGED, PIPE = 3, 9            # mia_debug_last_path: serial box-staged kernel (field by LDG) / pipelined kernel (field by TMA)
 
 
 def _case(shape, sp, seed):
@@ -116,7 +117,8 @@ def test_deformable_operators_follow_the_reference_recipe(cuda_device):
 @pytest.mark.parametrize("mode", ["itk", "vtk"])
 @pytest.mark.parametrize("kind", ["smooth", "tear", "far"])
 def test_box_staged_warp_matches_oracle(cuda_device, dtype, mode, kind):
-    """Row pitches the TMA unit accepts take the box-staged kernel (path 3): smooth fields stay inside the box, a field
+    """Row pitches the TMA unit accepts take the box-staged, software-pipelined kernel (path 9: image box AND field tile
+    by TMA): smooth fields stay inside the box, a field
     with a tear sends the affected tiles to the per-voxel gather, a field that points out of the volume gives
     background -- all against the oracle, and equal to the direct kernel up to float32 coordinate rounding."""
     from medicalimageanalysis_b200 import _lib
@@ -132,7 +134,7 @@ def test_box_staged_warp_matches_oracle(cuda_device, dtype, mode, kind):
         field[:, :5, :, 1] -= 2.0 * sp[1]                            # and a strip straddles the lower y border
     t, f = torch.from_numpy(img).to(cuda_device), torch.from_numpy(field).to(cuda_device)
     got = kernels.warp_dvf(t, f, A, B, background=-3001.0, mode=mode).cpu().numpy()
-    assert _lib.load().mia_debug_last_path() == 3
+    assert _lib.load().mia_debug_last_path() == PIPE
     want = D.oracle_warp_dvf(img, field, A, B, background=-3001.0, mode=mode)
     edge = (got == -3001) != (want == -3001)
     assert edge.mean() < 1e-4
@@ -153,7 +155,7 @@ def test_box_staged_warp_identity_translation_and_partial_tiles(cuda_device):
     t = torch.from_numpy(img).to(cuda_device)
     zero = torch.zeros(shape + (3,), dtype=torch.float32, device=cuda_device)
     assert torch.equal(kernels.warp_dvf(t, zero, A, B, mode="itk"), t)
-    assert _lib.load().mia_debug_last_path() == 3
+    assert _lib.load().mia_debug_last_path() == PIPE
     shift = np.array([2.0, -3.0, 5.0], dtype=np.float32)
     const = torch.from_numpy(np.broadcast_to(shift, shape + (3,)).copy()).to(cuda_device)
     As = A.copy()
@@ -174,12 +176,103 @@ def test_box_staged_warp_oblique_field_axes(cuda_device, dtype):
     field = _smooth_field(shape, 5.0, 19)
     got = kernels.warp_dvf(torch.from_numpy(img).to(cuda_device), torch.from_numpy(field).to(cuda_device), A, B2,
                            background=-3001.0, mode="itk").cpu().numpy()
-    assert _lib.load().mia_debug_last_path() == 3
+    assert _lib.load().mia_debug_last_path() == PIPE
     want = D.oracle_warp_dvf(img, field, A, B2, background=-3001.0, mode="itk")
     edge = (got == -3001) != (want == -3001)
     assert edge.mean() < 1e-4
     if dtype == np.int16:
         d = np.abs(got.astype(np.int32) - want.astype(np.int32))
         assert d[~edge].max() <= 1 and (d[~edge] > 0).mean() < 2e-3
+    else:
+        assert np.allclose(got[~edge], want[~edge], rtol=1e-4, atol=1e-2)
+
+
+@pytest.mark.parametrize("dtype", [np.int16, np.float32])
+@pytest.mark.parametrize("ox", [70, 61, 72])
+def test_field_lattice_other_than_the_image_lattice(cuda_device, dtype, ox):
+    """The field lives on the REFERENCE lattice (Deformable.create_image warps the moving image onto it), narrower and
+    shorter than the image here.  A field row of ox * 12 bytes is a TMA stride only when ox % 4 == 0: 72 takes the
+    pipelined kernel, 70 and 61 the serial one with the field read by LDG -- same oracle, same tolerance."""
+    from medicalimageanalysis_b200 import _lib
+    shape, sp = (40, 56, 96), (1.0, 1.1, 2.0)
+    oshape = (29, 50, ox)
+    g = G.Grid((shape[2], shape[1], shape[0]), sp, tuple(-0.5 * np.array(sp) * np.array(shape[::-1])))
+    og = G.Grid((oshape[2], oshape[1], oshape[0]), sp, (-0.5 * sp[0] * shape[2] + 7.3, -0.5 * sp[1] * shape[1] + 2.2, -0.5 * sp[2] * shape[0] + 5.0))
+    w2p = G.physical_to_index(g, "itk")
+    A, B = (w2p @ G.index_to_physical(og, "itk"))[:3], w2p[:3, :3]
+    img = make_phantom(shape, "CT", seed=21, spacing=sp).astype(dtype)
+    field = _smooth_field(oshape, 4.0, 22)
+    got = kernels.warp_dvf(torch.from_numpy(img).to(cuda_device), torch.from_numpy(field).to(cuda_device), A, B,
+                           background=-3001.0, mode="itk").cpu().numpy()
+    assert _lib.load().mia_debug_last_path() == (PIPE if ox % 4 == 0 else STAGED)
+    want = D.oracle_warp_dvf(img, field, A, B, background=-3001.0, mode="itk")
+    edge = (got == -3001) != (want == -3001)
+    assert edge.mean() < 1e-4
+    if dtype == np.int16:
+        d = np.abs(got.astype(np.int32) - want.astype(np.int32))
+        assert d[~edge].max() <= 1 and (d[~edge] > 0).mean() < 2e-3
+    else:
+        assert np.allclose(got[~edge], want[~edge], rtol=1e-4, atol=1e-2)
+
+
+@pytest.mark.parametrize("dtype", [np.int16, np.float32])
+@pytest.mark.parametrize("oshape", [(8, 8, 32), (3, 5, 8), (17, 8, 64), (64, 24, 96), (200, 104, 160)])
+def test_pipelined_warp_on_one_two_three_and_many_tiles_per_cta(cuda_device, dtype, oshape):
+    """The pipeline's prologue requests two field tiles and one box ahead; lattices of 1, 1 (partial), 6, 72 and 3250
+    tiles give CTAs with one, two, three and ten tiles (every buffer and barrier phase comes round)."""
+    from medicalimageanalysis_b200 import _lib
+    shape, sp = (200, 112, 168), (1.0, 1.0, 1.0)
+    g = G.Grid((shape[2], shape[1], shape[0]), sp, (0.0, 0.0, 0.0))
+    og = G.Grid((oshape[2], oshape[1], oshape[0]), sp, (3.25, 2.5, 0.75))
+    w2p = G.physical_to_index(g, "itk")
+    A, B = (w2p @ G.index_to_physical(og, "itk"))[:3], w2p[:3, :3]
+    z, y, x = np.meshgrid(*(np.arange(n, dtype=np.float32) for n in shape), indexing="ij")
+    img = (500 * np.sin(x / 7) * np.cos(y / 9) + 300 * np.sin(z / 5)).astype(dtype)
+    field = _smooth_field(oshape, 3.0, 23)
+    got = kernels.warp_dvf(torch.from_numpy(img).to(cuda_device), torch.from_numpy(field).to(cuda_device), A, B,
+                           background=-3001.0, mode="itk").cpu().numpy()
+    assert _lib.load().mia_debug_last_path() == PIPE
+    want = D.oracle_warp_dvf(img, field, A, B, background=-3001.0, mode="itk")
+    edge = (got == -3001) != (want == -3001)
+    assert edge.mean() < 1e-4
+    if dtype == np.int16:
+        d = np.abs(got.astype(np.int32) - want.astype(np.int32))
+        assert d[~edge].max() <= 1 and (d[~edge] > 0).mean() < 2e-3
+    else:
+        assert np.allclose(got[~edge], want[~edge], rtol=1e-4, atol=1e-2)
+
+
+@pytest.mark.parametrize("dtype", [np.int16, np.float32])
+@pytest.mark.parametrize("ox", [96, 70])
+def test_nan_displacements_give_background(cuda_device, dtype, ox):
+    """A NaN in the field (a registration that diverged, an unwritten voxel) must not address anything: the column's
+    coordinate range keeps the NaN (min.NaN / max.NaN), the column fails the interior test, the voxel compares as
+    outside.  Both box-staged kernels (96: pipelined, 70: serial)."""
+    from medicalimageanalysis_b200 import _lib
+    shape, sp = (40, 56, 96), (1.0, 1.1, 2.0)
+    oshape = (40, 56, ox)
+    g = G.Grid((shape[2], shape[1], shape[0]), sp, (0.0, 0.0, 0.0))
+    og = G.Grid((oshape[2], oshape[1], oshape[0]), sp, (0.0, 0.0, 0.0))
+    w2p = G.physical_to_index(g, "itk")
+    A, B = (w2p @ G.index_to_physical(og, "itk"))[:3], w2p[:3, :3]
+    img = make_phantom(shape, "CT", seed=31, spacing=sp).astype(dtype)
+    field = _smooth_field(oshape, 2.0, 32)
+    rng = np.random.default_rng(33)
+    holes = rng.random(oshape) < 0.01
+    for c in range(3):                                               # single components, so that x, y and z ranges all see one
+        field[..., c][holes & (rng.integers(0, 3, oshape) == c)] = np.nan
+    field[10:14, 20:30, 40:60] = np.nan                              # and a block: whole columns and warps of NaN
+    got = kernels.warp_dvf(torch.from_numpy(img).to(cuda_device), torch.from_numpy(field).to(cuda_device), A, B,
+                           background=-3001.0, mode="itk").cpu().numpy()
+    assert _lib.load().mia_debug_last_path() == (PIPE if ox % 4 == 0 else STAGED)
+    bad = np.isnan(field).any(axis=-1)
+    assert bad.mean() > 0.01 and np.all(got[bad] == -3001)
+    want = D.oracle_warp_dvf(img, field, A, B, background=-3001.0, mode="itk")
+    assert np.all(want[bad] == -3001)
+    edge = (got == -3001) != (want == -3001)
+    assert edge.mean() < 1e-4
+    if dtype == np.int16:
+        d = np.abs(got.astype(np.int32) - want.astype(np.int32))
+        assert d[~edge].max() <= 1
     else:
         assert np.allclose(got[~edge], want[~edge], rtol=1e-4, atol=1e-2)
