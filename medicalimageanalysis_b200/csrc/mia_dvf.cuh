@@ -473,18 +473,18 @@ __device__ __forceinline__ void dvf_coords(const DvfParams &p, const DvfConsts &
 
 struct DvfBoxPlace { int bx0, by0, bz0; bool none, fits; };
 
+// CTA bounding box from the 8 per-warp boxes: lane w < 8 takes warp w's six numbers, six REDUX finish the job (every
+// thread reading all 48 numbers cost 52 instructions per thread and tile, 6 % of the kernel).
 template <typename TM, class BOX>
-__device__ __forceinline__ DvfBoxPlace dvf_place(const int (*sbox)[6])
+__device__ __forceinline__ DvfBoxPlace dvf_place(const int (*sbox)[6], int lane)
 {
     constexpr int xalign = 16 / (int)sizeof(TM);
     const int big = 0x7fffffff;
-    int bx0 = big, bx1 = -big, by0 = big, by1 = -big, bz0 = big, bz1 = -big;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) {
-        bx0 = min(bx0, sbox[w][0]); bx1 = max(bx1, sbox[w][1]);
-        by0 = min(by0, sbox[w][2]); by1 = max(by1, sbox[w][3]);
-        bz0 = min(bz0, sbox[w][4]); bz1 = max(bz1, sbox[w][5]);
-    }
+    const bool have = lane < 8;
+    const int *mine = sbox[lane & 7];
+    int bx0 = __reduce_min_sync(0xffffffffu, have ? mine[0] : big), bx1 = __reduce_max_sync(0xffffffffu, have ? mine[1] : -big);
+    const int by0 = __reduce_min_sync(0xffffffffu, have ? mine[2] : big), by1 = __reduce_max_sync(0xffffffffu, have ? mine[3] : -big);
+    const int bz0 = __reduce_min_sync(0xffffffffu, have ? mine[4] : big), bz1 = __reduce_max_sync(0xffffffffu, have ? mine[5] : -big);
     DvfBoxPlace b;
     b.none = bx0 == big;
     bx0 &= ~(xalign - 1);                                   // TMA: inner coordinate * element size = 0 mod 16 bytes
@@ -631,7 +631,7 @@ warp_dvf_pipe_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
     dvf_coords<CLOSED, DIAG>(p, c, fbuf0, walk, lane, warp, tileA, s_box[0]);
     walk.advance();
     __syncthreads();
-    placeA = dvf_place<TM, BOX>(s_box[0]);
+    placeA = dvf_place<TM, BOX>(s_box[0], lane);
     if (threadIdx.x == 0) {
         if (placeA.fits) request_box(placeA, 0u);
         if (t0 + 2 * g < ntiles) request_field(t0 + 2 * g, 0u);
@@ -655,7 +655,7 @@ warp_dvf_pipe_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
             // s_box[NB] complete, field buffer NB read by everyone, and box buffer NB (tile t - g) long done with
             __syncthreads();
             if (more) {
-                pn = dvf_place<TM, BOX>(s_box[NB]);
+                pn = dvf_place<TM, BOX>(s_box[NB], lane);
                 if (threadIdx.x == 0) {
                     if (pn.fits) request_box(pn, NB);
                     if (t + 3 * g < ntiles) request_field(t + 3 * g, NB);
@@ -666,7 +666,7 @@ warp_dvf_pipe_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_cons
             dvf_interp<TM, TO, CLOSED, BOX>(p, cur, pc, box_smem, smem_u32(&s_bar[0]), ph0);
             __syncthreads();      // the box is free, s_box[NB] is complete, field buffer NB has been read by everyone
             if (more) {
-                pn = dvf_place<TM, BOX>(s_box[NB]);
+                pn = dvf_place<TM, BOX>(s_box[NB], lane);
                 if (threadIdx.x == 0) {
                     if (pn.fits) request_box(pn, 0u);
                     if (t + 3 * g < ntiles) request_field(t + 3 * g, NB);
