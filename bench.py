@@ -660,37 +660,48 @@ def main():
     for i in range(W):
         step(i)
     path_taken = int(kernels._lib.load().mia_debug_last_path())
-    # One CUDA graph per ring slot: a step is then one graph replay (the same single kernel on the same buffers).  At
-    # N = 8 a slab kernel takes 40 us and the ctypes + tensor-map + launch path of an eager call 56 us: un-graphed, the
-    # timed region would measure the host, not the GPU.
+    # The K timed steps are ONE CUDA graph of K kernel launches (step i on ring slot i % ring), replayed once inside the
+    # timed region: at N = 8 a slab kernel takes ~30 us, while an eager call costs 56 us of ctypes + tensor-map + launch
+    # path and even one graph launch per step leaves ~9 us between kernels -- un-graphed, the timed region would measure
+    # the host.  (One graph per ring slot, replayed step by step between CUDA events, gives the per-kernel times below.)
     torch.cuda.synchronize(dev)
+    eager_step = step
     graphs = []
     for i in range(ring):
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
-            step(i)
+            eager_step(i)
         graphs.append(g)
+    whole = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(whole):
+        for i in range(K):
+            eager_step(i)
 
     def step(i):                                            # noqa: F811  (from here on a step is a graph replay)
         graphs[i % ring].replay()
 
     for i in range(2 * ring):                               # the first launch of a graph uploads it: not part of a step
         step(i)
+    for _ in range(2):
+        whole.replay()
     torch.cuda.synchronize(dev)
     sampler = ClockSampler(local_rank)
     barrier()
     sampler.start()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
+    whole.replay()                                          # EXACTLY K steps
+    e1.record()
+    barrier()
+    total_ms = own_total_ms = e0.elapsed_time(e1)
+    # per-kernel times: the same K steps, one graph launch each, a CUDA event on both sides of every step
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
     for i in range(K):
         ev[i][0].record()
         step(i)
         ev[i][1].record()
-    e1.record()
-    barrier()
-    total_ms = e0.elapsed_time(e1)
+    torch.cuda.synchronize(dev)
     kernel_ms = [a.elapsed_time(b) for a, b in ev]
     # keep the GPU busy a little longer so the clock sampler sees load even for a very short timed region
     t_end = time.perf_counter() + 0.6
@@ -843,7 +854,8 @@ def main():
 
     if rank == 0:
         value = nvox_out * K / (total_ms * 1e-3) / 1e9
-        kavg = statistics.mean(kernel_ms) * 1e-3
+        # average launch duration over the timed region (this rank's K back-to-back launches, CUDA events on both sides)
+        kavg = own_total_ms / K * 1e-3
         alg_bytes = float(in_bytes + out_bytes)             # N_m*b_m + N_o*b_o of this rank's launch, int16 both
         achieved = alg_bytes / kavg / 1e9
         traffic, traffic_src = ncu_traffic() if world == 1 else (None, "captured at N = 1 only")
@@ -864,7 +876,10 @@ def main():
                          "kernel": "tile_x2_kernel<vtk, Box<128,16,12>> (TMA-staged x-pair tile kernel, csrc/mia_tile_x2.cuh)"
                          if path_taken == 5 else "path %d" % path_taken,
                          "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms_avg": kavg * 1e3,
-                         "kernel_ms_min": min(kernel_ms), "of_rank": 0, "launch": launch, "parity_c2": parity},
+                         "kernel_ms_single_launch_avg": statistics.mean(kernel_ms), "kernel_ms_single_launch_min": min(kernel_ms),
+                         "timing": "kernel_ms_avg = the timed region (one graph of K launches) / K; single_launch = the same "
+                                   "steps launched one graph at a time with an event on both sides of each",
+                         "of_rank": 0, "launch": launch, "parity_c2": parity},
             "cpu_baseline": cpu_line,
         }
         if parity is not None:

@@ -61,6 +61,26 @@ def main():
     r["path"] = int(lib.mia_debug_last_path())
     r["identical_to_whole"] = bool(torch.equal(o8[0], outs[0][k0:k0 + nz8]))
     out["c2_slab_of_8"] = r
+    # the same slabs as ONE graph of 20 launches (what bench.py replays at N > 1): no host launch path between kernels
+    for parts in (8, 4, 2):
+        nzp = (dims[2] + 7) // 8 // parts * 8
+        kp = min((parts // 2) * nzp, (dims[2] - nzp) // 8 * 8)
+        Ap = np.array(A, dtype=np.float64).reshape(3, 4).copy()
+        Ap[:, 3] += Ap[:, 2] * kp
+        op = [torch.empty((nzp, dims[1], dims[0]), dtype=torch.int16, device=dev) for _ in range(3)]
+        side = torch.cuda.Stream(dev)
+        with torch.cuda.stream(side):
+            for i in range(3):
+                kernels.resample(movs[i], Ap, (nzp, dims[1], dims[0]), background=-3001.0, mode="vtk", out=op[i])
+            side.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=side):
+                for i in range(21):
+                    kernels.resample(movs[i % 3], Ap, (nzp, dims[1], dims[0]), background=-3001.0, mode="vtk", out=op[i % 3])
+        torch.cuda.synchronize()
+        r = timeit(graph.replay, n=10, warm=3)
+        out["c2_slab_of_%d_graph" % parts] = {"us_per_launch": r["us_med"] / 21, "planes": nzp,
+                                               "identical_to_whole": bool(torch.equal(op[0], outs[0][kp:kp + nzp]))}
     if os.environ.get("K2_DEV_ONLY_C2"):
         print(json.dumps(out))
         return
