@@ -181,7 +181,10 @@ int mia_optimizer_read(const void *d_state, double params[6], double *scale, int
  * one physical displacement (x, y, z) per OUTPUT voxel, float32, reference layout [z][y][x][3] (self.dvf,
  * deformable.py:797).  Output voxel idx is sampled at moving index  A . (idx, 1) + B . d :
  * A = W2P_image . P2W_out (3x4, row-major), B = linear part of W2P_image (3x3, row-major).  Inside rule,
- * rounding and background as mia_resample_rigid; the output keeps the image's pixel type.
+ * rounding and background as mia_resample_rigid; the output keeps the image's pixel type.  A displacement that is
+ * NaN gives the background value.  Any sizes and pitches work; the fast kernel (image box and field tile staged by
+ * TMA) needs an image row and a field row that are multiples of 16 bytes (odims[0] % 4 == 0 for the field) and
+ * 16-byte aligned base pointers.
  */
 int mia_warp_dvf(const void *d_mov, int mov_dtype, const int mdims[3], const float *d_dvf, void *d_out, int out_dtype,
                  const int odims[3], const double A[12], const double B[9], double background, int mode, void *stream);
