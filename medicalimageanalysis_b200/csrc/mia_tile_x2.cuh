@@ -360,7 +360,7 @@ tile_x2_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__
     // (p.ws_ticket: {next tile, CTAs that are done}) a CTA takes the next chunk whenever its producer has room for one,
     // so a CTA that drew cheap tiles (background corners) simply takes more of them; without one the chunks go round-robin.
     // Static round-robin left ~11 % of the SM time idle at the end of config 2 (90 tiles per CTA of cost 0.1 .. 1.4:
-    // the slowest of 296 sums sets the time), and far more on a z-slab of it (11 tiles per CTA on 8 GPUs).
+    // the slowest of 296 sums sets the time): 201 -> 189 us.
     // (A guided tail -- the last chunk per CTA worth of tiles claimed ONE at a time from a second counter -- was measured
     // on config 2 and on its z-slabs of 2 / 4 / 8 replayed as graphs: no gain, 1-2 us lost with a longer tail zone.  A
     // slab kernel of an 8-GPU job runs 31 us where an eighth of the whole launch would be 24: the difference is the
