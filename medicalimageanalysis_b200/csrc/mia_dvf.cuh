@@ -540,6 +540,12 @@ __device__ __forceinline__ void dvf_interp(const DvfParams &p, const DvfTile &st
             const f32x2 wx2 = sub2(lx2, sub2(tx2, magic2)), wy2 = sub2(ly2, sub2(ty2, magic2)), wz2 = sub2(lz2, sub2(tz2, magic2));
             const uint32_t a0 = mad_u32(mad_u32(mad_u32((uint32_t)tz2, BOX::kY, (uint32_t)ty2), BOX::kX, (uint32_t)tx2), ES, ubase);
             const uint32_t a1 = mad_u32(mad_u32(mad_u32((uint32_t)(tz2 >> 32), BOX::kY, (uint32_t)(ty2 >> 32)), BOX::kX, (uint32_t)(tx2 >> 32)), ES, ubase);
+#ifdef MIA_BOUNDS_CHECK
+            // Debug build (compute-sanitizer is closed on this pool): all 8 taps of both voxels inside the staged box
+            if (a0 < box_smem || a0 + PZ + PY + 2u * ES > box_smem + BOX::kX * BOX::kY * BOX::kZ * ES ||
+                a1 < box_smem || a1 + PZ + PY + 2u * ES > box_smem + BOX::kX * BOX::kY * BOX::kZ * ES)
+                __trap();
+#endif
             const f32x2 v000 = pk(Tap<TM, 0>::ld(a0), Tap<TM, 0>::ld(a1));
             const f32x2 v100 = pk(Tap<TM, ES>::ld(a0), Tap<TM, ES>::ld(a1));
             const f32x2 v010 = pk(Tap<TM, PY>::ld(a0), Tap<TM, PY>::ld(a1));
