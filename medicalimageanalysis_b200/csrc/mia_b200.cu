@@ -613,7 +613,10 @@ int x2_claim_slot(cudaStream_t s, unsigned **claim)
     }
     if (!b) return MIA_OK;
     cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
-    CUDA_TRY(cudaStreamIsCapturing(s, &st));
+    if (cudaStreamIsCapturing(s, &st) != cudaSuccess) {     // e.g. the legacy stream while another stream captures:
+        cudaGetLastError();                                 // not this function's business -- deal the tiles statically
+        return MIA_OK;
+    }
     if (st == cudaStreamCaptureStatusNone) {
         *claim = b + 2u * (seq_eager.fetch_add(1u) % kX2EagerSlots);
     } else {
